@@ -1,0 +1,277 @@
+"""Keras-style training callbacks: base class, History, progress bar, ModelCheckpoint,
+TensorBoard.
+
+Reference use: rank-0-only ``ModelCheckpoint('checkpoint-{epoch}.h5')`` and
+``TensorBoard(log_dir, update_freq='batch')`` (``mnist_keras.py:101-105``,
+``tensorflow2_keras_mnist.py:86-89``), ``verbose=1`` only on rank 0
+(``mnist_keras.py:111``, ``tensorflow2_keras_mnist.py:92``).
+
+Log values may be 0-dim device tensors; a callback calls ``float(v)`` only when it
+really needs the number, so nothing here forces a device sync every step unless the
+user asked for per-batch output (``update_freq='batch'`` does, as in the reference).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+from typing import Dict, List, Optional
+
+
+class Callback:
+    def __init__(self):
+        self.model = None
+        self.params: Dict = {}
+
+    def set_model(self, model):
+        self.model = model
+
+    def set_params(self, params):
+        self.params = params
+
+    def on_train_begin(self, logs=None): ...
+    def on_train_end(self, logs=None): ...
+    def on_epoch_begin(self, epoch, logs=None): ...
+    def on_epoch_end(self, epoch, logs=None): ...
+    def on_batch_begin(self, batch, logs=None): ...
+    def on_batch_end(self, batch, logs=None): ...
+    # tf.keras spellings
+    def on_train_batch_begin(self, batch, logs=None):
+        self.on_batch_begin(batch, logs)
+
+    def on_train_batch_end(self, batch, logs=None):
+        self.on_batch_end(batch, logs)
+
+
+class CallbackList:
+    """Calls callbacks *in list order* - the order matters: MetricAverage must run before
+    any metrics-consuming callback (``tensorflow2_keras_mnist.py:73-76``)."""
+
+    def __init__(self, callbacks: List[Callback], model, params):
+        self.callbacks = list(callbacks)
+        for c in self.callbacks:
+            c.set_model(model)
+            c.set_params(params)
+
+    def _call(self, hook, *a):
+        for c in self.callbacks:
+            getattr(c, hook)(*a)
+
+    def on_train_begin(self, logs=None): self._call("on_train_begin", logs)
+    def on_train_end(self, logs=None): self._call("on_train_end", logs)
+    def on_epoch_begin(self, e, logs=None): self._call("on_epoch_begin", e, logs)
+    def on_epoch_end(self, e, logs=None): self._call("on_epoch_end", e, logs)
+    def on_batch_begin(self, b, logs=None): self._call("on_train_batch_begin", b, logs)
+    def on_batch_end(self, b, logs=None): self._call("on_train_batch_end", b, logs)
+
+
+class History(Callback):
+    def on_train_begin(self, logs=None):
+        self.epoch: List[int] = []
+        self.history: Dict[str, List[float]] = {}
+
+    def on_epoch_end(self, epoch, logs=None):
+        self.epoch.append(epoch)
+        for k, v in (logs or {}).items():
+            self.history.setdefault(k, []).append(float(v))
+
+
+class ProgbarLogger(Callback):
+    """``verbose=1`` progress output.  Prints at most every ``interval`` seconds so the
+    device is not synced every step."""
+
+    def __init__(self, interval: float = 0.5, stream=None):
+        super().__init__()
+        self.interval = interval
+        self.stream = stream or sys.stdout
+
+    def on_epoch_begin(self, epoch, logs=None):
+        self.stream.write(f"Epoch {epoch + 1}/{self.params.get('epochs', '?')}\n")
+        self._t0 = self._last = time.time()
+        self._seen = 0
+
+    def _fmt(self, logs):
+        return " - ".join(f"{k}: {float(v):.4f}" for k, v in logs.items()
+                          if k not in ("batch", "size"))
+
+    def on_batch_end(self, batch, logs=None):
+        self._seen = batch + 1
+        now = time.time()
+        if now - self._last >= self.interval:
+            self._last = now
+            steps = self.params.get("steps")
+            self.stream.write(f"\r{self._seen}/{steps if steps else '?'} - {self._fmt(logs or {})}")
+            self.stream.flush()
+
+    def on_epoch_end(self, epoch, logs=None):
+        steps = self.params.get("steps") or self._seen
+        dt = time.time() - self._t0
+        self.stream.write(f"\r{steps}/{steps} - {dt:.0f}s - {self._fmt(logs or {})}\n")
+        self.stream.flush()
+
+
+class ModelCheckpoint(Callback):
+    """Keras defaults: ``save_weights_only=False, save_best_only=False, period=1`` - a
+    full-model HDF5 file every epoch, 1-based epoch number in the name
+    (``checkpoint-1.h5`` first)."""
+
+    def __init__(self, filepath, monitor="val_loss", verbose=0, save_best_only=False,
+                 save_weights_only=False, mode="auto", period=1):
+        super().__init__()
+        self.filepath = filepath
+        self.monitor = monitor
+        self.verbose = verbose
+        self.save_best_only = save_best_only
+        self.save_weights_only = save_weights_only
+        self.period = period
+        self._since = 0
+        if mode == "max" or (mode == "auto" and ("acc" in monitor or monitor.startswith("fmeasure"))):
+            self._better, self.best = (lambda a, b: a > b), -float("inf")
+        else:
+            self._better, self.best = (lambda a, b: a < b), float("inf")
+
+    def on_epoch_end(self, epoch, logs=None):
+        logs = logs or {}
+        self._since += 1
+        if self._since < self.period:
+            return
+        self._since = 0
+        path = self.filepath.format(epoch=epoch + 1, **{k: float(v) for k, v in logs.items()})
+        if self.save_best_only:
+            cur = logs.get(self.monitor)
+            if cur is None or not self._better(float(cur), self.best):
+                return
+            self.best = float(cur)
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        if self.save_weights_only:
+            self.model.save_weights(path)
+        else:
+            self.model.save(path)
+        if self.verbose:
+            print(f"\nEpoch {epoch + 1:05d}: saving model to {path}")
+
+
+class TensorBoard(Callback):
+    """Writes TF event files (own writer, ``utils/tfevents.py``) with the same scalar tags
+    Keras uses: per-batch ``batch_loss``/``batch_<metric>`` when ``update_freq='batch'``,
+    per-epoch ``epoch_loss``, ``epoch_<metric>``, ``epoch_val_*`` and ``epoch_lr``.
+
+    Every scalar is mirrored to the metrics sink (``utils/metrics_sink.py``), which is the
+    local stand-in for ``gradient_utils.metrics.init(sync_tensorboard=True)``
+    (``mnist_keras.py:22-23``)."""
+
+    def __init__(self, log_dir="./logs", update_freq="epoch", histogram_freq=0, write_graph=False,
+                 **_ignored):
+        super().__init__()
+        self.log_dir = log_dir
+        self.update_freq = update_freq
+        self._writer = None
+        self._val_writer = None
+        self._step = 0
+
+    def _w(self):
+        if self._writer is None:
+            from ..utils.tfevents import EventWriter
+            self._writer = EventWriter(os.path.join(self.log_dir, "train"))
+        return self._w_cached()
+
+    def _w_cached(self):
+        return self._writer
+
+    def _vw(self):
+        if self._val_writer is None:
+            from ..utils.tfevents import EventWriter
+            self._val_writer = EventWriter(os.path.join(self.log_dir, "validation"))
+        return self._val_writer
+
+    def _emit(self, writer, tag, value, step):
+        from ..utils import metrics_sink
+        v = float(value)
+        writer.add_scalar(tag, v, step)
+        metrics_sink.record(tag, v, step)
+
+    def on_batch_end(self, batch, logs=None):
+        self._step += 1
+        if self.update_freq == "batch" or (isinstance(self.update_freq, int)
+                                           and self._step % self.update_freq == 0):
+            w = self._w()
+            for k, v in (logs or {}).items():
+                if k in ("batch", "size"):
+                    continue
+                self._emit(w, "batch_" + k, v, self._step)
+
+    def on_epoch_end(self, epoch, logs=None):
+        for k, v in (logs or {}).items():
+            if k.startswith("val_"):
+                self._emit(self._vw(), "epoch_" + k[4:], v, epoch)
+            else:
+                self._emit(self._w(), "epoch_" + k, v, epoch)
+        self.flush()
+
+    def flush(self):
+        for w in (self._writer, self._val_writer):
+            if w is not None:
+                w.flush()
+
+    def on_train_end(self, logs=None):
+        for w in (self._writer, self._val_writer):
+            if w is not None:
+                w.close()
+        self._writer = self._val_writer = None
+
+
+class LambdaCallback(Callback):
+    def __init__(self, **hooks):
+        super().__init__()
+        for k, fn in hooks.items():
+            if fn is not None:
+                setattr(self, k, fn)
+
+
+class EarlyStopping(Callback):
+    def __init__(self, monitor="val_loss", min_delta=0.0, patience=0, mode="min"):
+        super().__init__()
+        self.monitor, self.min_delta, self.patience = monitor, min_delta, patience
+        self.sign = 1.0 if mode == "min" else -1.0
+
+    def on_train_begin(self, logs=None):
+        self.best, self.wait = float("inf"), 0
+
+    def on_epoch_end(self, epoch, logs=None):
+        cur = (logs or {}).get(self.monitor)
+        if cur is None:
+            return
+        cur = self.sign * float(cur)
+        if cur < self.best - self.min_delta:
+            self.best, self.wait = cur, 0
+        else:
+            self.wait += 1
+            if self.wait > self.patience:
+                self.model.stop_training = True
+
+
+class ReduceLROnPlateau(Callback):
+    """Included because the reference's comment names it as a metrics-consuming callback
+    that must come after MetricAverage (``tensorflow2_keras_mnist.py:75``)."""
+
+    def __init__(self, monitor="val_loss", factor=0.1, patience=10, min_lr=0.0, min_delta=1e-4):
+        super().__init__()
+        self.monitor, self.factor, self.patience = monitor, factor, patience
+        self.min_lr, self.min_delta = min_lr, min_delta
+
+    def on_train_begin(self, logs=None):
+        self.best, self.wait = float("inf"), 0
+
+    def on_epoch_end(self, epoch, logs=None):
+        cur = (logs or {}).get(self.monitor)
+        if cur is None:
+            return
+        cur = float(cur)
+        if cur < self.best - self.min_delta:
+            self.best, self.wait = cur, 0
+            return
+        self.wait += 1
+        if self.wait >= self.patience:
+            opt = self.model.optimizer
+            opt.lr = max(opt.lr * self.factor, self.min_lr)
+            self.wait = 0

@@ -1,0 +1,192 @@
+"""A small ``tf.data``-like pipeline and array batching.
+
+Reference use (``tensorflow2_keras_mnist.py:37-41``)::
+
+    dataset = tf.data.Dataset.from_tensor_slices((images, labels))
+    dataset = dataset.repeat().shuffle(10000).batch(128)
+
+Only the operators the reference touches are provided (plus ``take``/``map``).  The
+pipeline works on *indices* - a repeat/shuffle-buffer/batch stream of row indices - and
+gathers rows from the source arrays once per batch, so a batch costs one fancy-index
+per array.  Batches are produced into pinned host memory when CUDA is available so the
+trainer's per-step H2D copy is asynchronous.
+"""
+from __future__ import annotations
+
+from typing import Callable, Iterator, Optional, Sequence, Tuple
+
+import numpy as np
+
+
+class Dataset:
+    def __init__(self, arrays: Tuple[np.ndarray, ...]):
+        n = len(arrays[0])
+        for a in arrays:
+            if len(a) != n:
+                raise ValueError("all arrays must share the first dimension")
+        self._arrays = tuple(np.asarray(a) for a in arrays)
+        self._n = n
+        self._ops = []          # list of (op, arg)
+        self._seed = None
+
+    @staticmethod
+    def from_tensor_slices(tensors) -> "Dataset":
+        if isinstance(tensors, (tuple, list)):
+            return Dataset(tuple(_to_numpy(t) for t in tensors))
+        return Dataset((_to_numpy(tensors),))
+
+    def _derive(self, op, arg) -> "Dataset":
+        d = Dataset.__new__(Dataset)
+        d._arrays, d._n, d._seed = self._arrays, self._n, self._seed
+        d._ops = self._ops + [(op, arg)]
+        return d
+
+    def repeat(self, count: Optional[int] = None) -> "Dataset":
+        return self._derive("repeat", count)
+
+    def shuffle(self, buffer_size: int, seed: Optional[int] = None) -> "Dataset":
+        d = self._derive("shuffle", int(buffer_size))
+        if seed is not None:
+            d._seed = seed
+        return d
+
+    def batch(self, batch_size: int, drop_remainder: bool = False) -> "Dataset":
+        return self._derive("batch", (int(batch_size), drop_remainder))
+
+    def take(self, count: int) -> "Dataset":
+        return self._derive("take", int(count))
+
+    def map(self, fn: Callable) -> "Dataset":
+        return self._derive("map", fn)
+
+    @property
+    def cardinality(self) -> int:
+        """Number of elements produced, or -1 if infinite."""
+        n = self._n
+        for op, arg in self._ops:
+            if op == "repeat":
+                if arg is None:
+                    return -1
+                n *= arg
+            elif op == "batch":
+                bs, drop = arg
+                if n >= 0:
+                    n = n // bs if drop else -(-n // bs)
+            elif op == "take":
+                n = arg if n < 0 else min(n, arg)
+        return n
+
+    # -- index stream ----------------------------------------------------------
+    def _index_stream(self, rng) -> Iterator:
+        def base():
+            for i in range(self._n):
+                yield i
+        stream = base()
+        batched = False
+        maps = []
+        for op, arg in self._ops:
+            if op == "repeat":
+                stream = _repeat(self, stream, arg, self._ops, rng)
+            elif op == "shuffle":
+                stream = _shuffle(stream, arg, rng)
+            elif op == "batch":
+                stream = _batch(stream, *arg)
+                batched = True
+            elif op == "take":
+                stream = _take(stream, arg)
+            elif op == "map":
+                maps.append(arg)
+        return stream, batched, maps
+
+    def __iter__(self):
+        rng = np.random.default_rng(self._seed)
+        stream, batched, maps = self._index_stream(rng)
+        for idx in stream:
+            if batched:
+                idx = np.asarray(idx, dtype=np.int64)
+            out = tuple(a[idx] for a in self._arrays)
+            for fn in maps:
+                out = fn(*out)
+                if not isinstance(out, tuple):
+                    out = (out,)
+            yield out if len(out) > 1 else out[0]
+
+
+def _repeat(ds, stream, count, ops, rng):
+    # ``repeat`` restarts everything upstream of it; upstream here is always the plain
+    # range (the reference calls repeat() first), so restart the base range.
+    first = True
+    n = 0
+    while count is None or n < count:
+        if first:
+            yield from stream
+            first = False
+        else:
+            yield from range(ds._n)
+        n += 1
+
+
+def _shuffle(stream, buffer_size, rng):
+    buf = []
+    for i in stream:
+        if len(buf) < buffer_size:
+            buf.append(i)
+            continue
+        j = int(rng.integers(0, buffer_size))
+        out, buf[j] = buf[j], i
+        yield out
+    rng.shuffle(buf)
+    yield from buf
+
+
+def _batch(stream, bs, drop):
+    cur = []
+    for i in stream:
+        cur.append(i)
+        if len(cur) == bs:
+            yield cur
+            cur = []
+    if cur and not drop:
+        yield cur
+
+
+def _take(stream, n):
+    for k, i in enumerate(stream):
+        if k >= n:
+            return
+        yield i
+
+
+def _to_numpy(t):
+    try:
+        import torch
+        if isinstance(t, torch.Tensor):
+            return t.detach().cpu().numpy()
+    except ImportError:  # pragma: no cover
+        pass
+    return np.asarray(t)
+
+
+class ArrayBatcher:
+    """Keras ``fit(x, y, batch_size, shuffle=True)`` batching: a fresh permutation every
+    epoch and a partial last batch (60000 = 468*128 + 96)."""
+
+    def __init__(self, arrays: Sequence[np.ndarray], batch_size: int, shuffle: bool, seed=None):
+        self.arrays = [np.asarray(a) for a in arrays]
+        self.n = len(self.arrays[0])
+        self.batch_size = int(batch_size)
+        self.shuffle = shuffle
+        self.rng = np.random.default_rng(seed)
+
+    @property
+    def steps(self) -> int:
+        return -(-self.n // self.batch_size)
+
+    def epoch(self):
+        order = self.rng.permutation(self.n) if self.shuffle else None
+        for s in range(0, self.n, self.batch_size):
+            if order is None:
+                yield tuple(a[s:s + self.batch_size] for a in self.arrays)
+            else:
+                idx = np.sort(order[s:s + self.batch_size]) if False else order[s:s + self.batch_size]
+                yield tuple(a[idx] for a in self.arrays)

@@ -1,0 +1,30 @@
+"""BASELINE.json config 2: world_size=2 on CPU/gloo - broadcast + metric-average plumbing."""
+import pytest
+
+from conftest import run_workers
+
+
+def _ok(outs):
+    for rc, out in outs:
+        assert rc == 0 and out.strip().endswith("OK"), out
+
+
+def test_collectives_ws2():
+    _ok(run_workers("collectives"))
+
+
+def test_collectives_ws3():
+    _ok(run_workers("collectives", world_size=3))
+
+
+def test_broadcast_and_average_gradients_ws2():
+    _ok(run_workers("broadcast_and_grads"))
+
+
+def test_tf2_script_flow_ws2(tmp_path):
+    _ok(run_workers("tf2_script_flow", env={"HVD_TEST_OUT": str(tmp_path)}))
+    assert (tmp_path / "tb" / "train").exists()
+
+
+def test_bucket_plan_mismatch_detected():
+    _ok(run_workers("plan_mismatch"))

@@ -1,0 +1,134 @@
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from horovod_distributed_example_b200 import keras
+from horovod_distributed_example_b200.parallel import buckets as B
+from horovod_distributed_example_b200.parallel.arena import ParamArena
+from horovod_distributed_example_b200.utils import metrics_sink, tfevents
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_tfevents_roundtrip_and_crc(tmp_path):
+    w = tfevents.EventWriter(str(tmp_path))
+    for i in range(5):
+        w.add_scalar("batch_loss", 1.0 / (i + 1), i)
+    w.add_scalar("epoch_accuracy", 0.75, 0)
+    w.close()
+    rec = tfevents.read_scalars(w.path)
+    assert [t for t, _, _ in rec] == ["batch_loss"] * 5 + ["epoch_accuracy"]
+    assert rec[3][1] == 3 and abs(rec[3][2] - 0.25) < 1e-7
+    raw = bytearray(open(w.path, "rb").read())
+    raw[-6] ^= 0xFF
+    open(w.path, "wb").write(raw)
+    with pytest.raises(ValueError):
+        tfevents.read_scalars(w.path)
+
+
+def test_crc32c_known_vector():
+    from horovod_distributed_example_b200.ops import native
+    assert native.core_lib().hvd_crc32c(b"123456789", 9) == 0xE3069283
+
+
+def test_bucket_planner_native_matches_python():
+    specs = [("d2/b", (10,)), ("d2/k", (128, 10)), ("d1/b", (128,)), ("d1/k", (9216, 128)),
+             ("c2/b", (64,)), ("c2/k", (3, 3, 32, 64)), ("c1/b", (32,)), ("c1/k", (3, 3, 1, 32))]
+    a = ParamArena(specs, "cpu")
+    offs = [s.offset for s in a.specs]; nums = [s.numel for s in a.specs]
+    for thr, cuts in [(64 << 20, []), (64 << 20, ["d1/k"]), (1 << 16, []), (4, []), (5 << 20, ["d2/k", "c2/b"])]:
+        nat = B.plan(a, thr, cuts)
+        py = B.plan_python(offs, nums, a.n, thr, [[s.name for s in a.specs].index(c) for c in cuts])
+        assert nat == py
+        assert nat[0].start == 0 and nat[-1].end == a.n
+        for x, y in zip(nat, nat[1:]):
+            assert x.end == y.start and y.first_tensor == x.last_tensor + 1
+    one = B.plan(a, 64 << 20)
+    assert len(one) == 1
+    two = B.plan(a, 64 << 20, ["d1/k"])
+    assert len(two) == 2 and two[0].last_tensor == 3
+    assert two[0].nbytes > 0.98 * 4 * a.n_params()        # dense1 kernel dominates (98.3% of bytes)
+    h1 = B.plan_hash([s.name for s in a.specs], [s.shape for s in a.specs], one)
+    h2 = B.plan_hash([s.name for s in a.specs], [s.shape for s in a.specs], two)
+    assert h1 != h2
+
+
+def test_arena_layout_and_checksum():
+    a = ParamArena([("x", (3, 5)), ("y", (70,))], "cpu", n_slots=2, double_grads=True)
+    assert a.spec("y").offset % 64 == 0 and a.n % 64 == 0
+    assert a.total == a.n * 5
+    a.param("x").fill_(1.0); a.grad("x", 1).fill_(2.0); a.slot(1, "y").fill_(3.0)
+    assert a.buffer[0] == 1 and a.buffer[a.grad_offset(1)] == 2 and a.buffer[a.slot_offset(1) + a.spec("y").offset] == 3
+    c1 = int(a.checksum()); a.param("y")[5] += 1e-6; assert int(a.checksum()) != c1
+
+
+def test_dataset_pipeline_semantics():
+    x = np.arange(10)[:, None].astype(np.float32); y = np.arange(10)
+    ds = keras.Dataset.from_tensor_slices((x, y)).repeat().shuffle(4, seed=0).batch(3)
+    assert ds.cardinality == -1
+    it = iter(ds)
+    got = np.concatenate([next(it)[1] for _ in range(10)])
+    assert len(got) == 30 and sorted(got[:10].tolist()) != got[:10].tolist()
+    for k in range(10):                       # the buffer (4) may pull a few items across epochs
+        assert 2 <= (got == k).sum() <= 4
+    fin = keras.Dataset.from_tensor_slices((x, y)).batch(4)
+    assert fin.cardinality == 3 and [len(b[0]) for b in fin] == [4, 4, 2]
+    assert keras.Dataset.from_tensor_slices((x, y)).repeat(2).batch(5, drop_remainder=True).cardinality == 4
+
+
+def test_to_categorical_and_synthetic_mnist():
+    oh = keras.utils.to_categorical([0, 2, 1], 3)
+    assert oh.tolist() == [[1, 0, 0], [0, 0, 1], [0, 1, 0]]
+    (xt, yt), (xe, ye) = keras.datasets.synthetic_mnist(256, 64)
+    assert xt.shape == (256, 28, 28) and xt.dtype == np.uint8 and ye.shape == (64,) and yt.max() <= 9
+
+
+def test_metrics_sink_ci_check(tmp_path):
+    metrics_sink.init(True, str(tmp_path / "m.jsonl"))
+    for i, v in enumerate([0.5, 0.2, 0.1]):
+        metrics_sink.record("epoch_loss", v, i)
+    ok = metrics_sink.check("tensorflow:loss", "0.0..0.3", "mean")
+    assert ok["passed"] and abs(ok["value"] - 0.8 / 3) < 1e-9
+    assert not metrics_sink.check("tensorflow:loss", "0.0..0.1", "mean")["passed"]
+    metrics_sink.close()
+    assert len(open(tmp_path / "m.jsonl").read().splitlines()) == 3
+    metrics_sink.init(False)
+
+
+def test_timeline_chrome_trace(tmp_path):
+    from horovod_distributed_example_b200.utils.timeline import Timeline
+    p = str(tmp_path / "tl.json")
+    t = Timeline(p, mark_cycles=True)
+    t.begin("grad.bucket0", "ALLREDUCE"); t.end("grad.bucket0", "ALLREDUCE")
+    t.complete("grad.bucket0", "FUSED_ALLREDUCE_UPDATE", 10, 25); t.mark_cycle(); t.close()
+    ev = json.load(open(p))
+    assert [e["ph"] for e in ev if e["name"] == "ALLREDUCE"] == ["B", "E"]
+    assert any(e["ph"] == "X" and e["dur"] == 25 for e in ev) and any(e["ph"] == "M" for e in ev)
+
+
+def test_launcher_kills_group_on_failure(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text("import os,sys,time\nr=int(os.environ['HVD_RANK'])\n"
+                      "assert os.environ['HVD_SIZE']=='3' and os.environ['FOO']=='bar'\n"
+                      "if r==1: sys.exit(7)\ntime.sleep(60)\n")
+    import time
+    t0 = time.time()
+    rc = subprocess.run([sys.executable, "-m", "horovod_distributed_example_b200.run", "-np", "3",
+                         "-x", "FOO=bar", str(script)], cwd=ROOT, capture_output=True, text=True)
+    assert rc.returncode == 7 and time.time() - t0 < 30
+    assert "rank 1 exited with code 7" in rc.stderr
+
+
+def test_launcher_env_contract(tmp_path):
+    script = tmp_path / "e.py"
+    script.write_text("import os\nopen(os.environ['OUT']+os.environ['HVD_RANK'],'w').write("
+                      "os.environ['HVD_LOCAL_RANK']+os.environ['MASTER_ADDR'])\n")
+    rc = subprocess.run([sys.executable, "-m", "horovod_distributed_example_b200.run", "-np", "2",
+                         "--allow-run-as-root", "-bind-to", "none", "-map-by", "slot", "-mca", "pml", "ob1",
+                         "-x", f"OUT={tmp_path}/r", str(script)], cwd=ROOT, capture_output=True, text=True)
+    assert rc.returncode == 0, rc.stderr
+    assert (tmp_path / "r0").read_text() == "0127.0.0.1" and (tmp_path / "r1").read_text() == "1127.0.0.1"
