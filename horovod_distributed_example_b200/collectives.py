@@ -71,7 +71,7 @@ def _use_peer(t: torch.Tensor) -> bool:
     if cfg is not None and cfg.allreduce_variant == "nccl":
         return False
     from .parallel import peer
-    return peer.available()
+    return _state.size > 1 and peer.available()
 
 
 def _fault_skip() -> bool:

@@ -1,0 +1,255 @@
+// Fused peer-memory collectives for sm_100a: allreduce + 1/N scale + optimizer update in ONE
+// kernel, reading and writing peer GPUs' arenas over NVLink 5 / NVSwitch from inside the kernel.
+//
+// Capability parity: this is the data path behind hvd.DistributedOptimizer (reference
+// mnist_keras.py:87, tensorflow2_keras_mnist.py:58), BroadcastGlobalVariablesCallback
+// (mnist_keras.py:97) and MetricAverageCallback (tensorflow2_keras_mnist.py:77).  Horovod 0.18.1
+// does memcpy-in -> ncclAllReduce(ring) -> memcpy-out -> divide -> ~10 optimizer kernels per
+// weight; here a gradient bucket is a contiguous arena range and each step is one launch.
+//
+// Variants (picked per message size from the measured table, parallel/variants.py):
+//   ONESHOT  every rank reads all N ranks' bucket, sums in fixed rank order (bit-identical on
+//            all ranks), updates its own replica.  (N-1)*S inbound; one barrier; latency-optimal.
+//   TWOSHOT  rank r owns shard r: reduce-scatter by peer loads, update the shard (optimizer state
+//            is sharded for these buckets), all-gather the UPDATED PARAMS by peer stores.
+//            2*S*(N-1)/N per GPU.
+//   NVLS     as TWOSHOT but the switch reduces (multimem.ld_reduce) and broadcasts (multimem.st):
+//            ~S/N in and S/N out per GPU.
+#include "comm.cuh"
+
+#include <cooperative_groups.h>
+#include <stdio.h>
+
+enum { HVD_ONESHOT = 0, HVD_TWOSHOT = 1, HVD_NVLS = 2 };
+enum { HVD_KIND_NONE = 0, HVD_KIND_SGD = 1, HVD_KIND_ADADELTA = 2, HVD_KIND_ADAM = 3 };
+// hyper vector layout (keras/optimizers.py)
+enum { H_LR = 0, H_A = 1, H_B = 2, H_EPS = 3, H_STEP = 4, H_DECAY = 5, H_LR_T = 6 };
+
+struct HvdFusedArgs {
+  long long start, end;                                   // element range in the slab (multiples of 4)
+  long long grad_off, param_off, slot0_off, slot1_off;    // slab offsets inside the symmetric buffer
+  long long out_off;                                      // KIND_NONE: where the averaged result goes
+  const float* hyper;                                     // device fp32[8]
+  float scale;                                            // 1/N (average) or 1 (sum)
+  int kind, variant, slot, exit_barrier;
+};
+
+template <int KIND>
+__device__ __forceinline__ float update_one(float g, float p, float& s0, float& s1, const float* __restrict__ h) {
+  if (KIND == HVD_KIND_ADADELTA) {
+    const float rho = h[H_A], eps = h[H_EPS];
+    s0 = rho * s0 + (1.0f - rho) * g * g;
+    const float u = g * sqrtf(s1 + eps) / sqrtf(s0 + eps);
+    s1 = rho * s1 + (1.0f - rho) * u * u;
+    return p - h[H_LR] * u;
+  } else if (KIND == HVD_KIND_ADAM) {
+    const float b1 = h[H_A], b2 = h[H_B];
+    s0 = b1 * s0 + (1.0f - b1) * g;
+    s1 = b2 * s1 + (1.0f - b2) * g * g;
+    return p - h[H_LR_T] * s0 / (sqrtf(s1) + h[H_EPS]);
+  } else if (KIND == HVD_KIND_SGD) {
+    const float mom = h[H_A];
+    s0 = mom * s0 - h[H_LR] * g;
+    return (h[H_B] != 0.0f) ? p + mom * s0 - h[H_LR] * g : p + s0;
+  }
+  return g;
+}
+
+template <int KIND>
+__device__ __forceinline__ float4 update_f4(float4 g, float* p_ptr, float* s0_ptr, float* s1_ptr,
+                                            const float* __restrict__ h) {
+  float4 p = *reinterpret_cast<float4*>(p_ptr);
+  float4 s0 = *reinterpret_cast<float4*>(s0_ptr);
+  float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (KIND != HVD_KIND_SGD) s1 = *reinterpret_cast<float4*>(s1_ptr);
+  p.x = update_one<KIND>(g.x, p.x, s0.x, s1.x, h);
+  p.y = update_one<KIND>(g.y, p.y, s0.y, s1.y, h);
+  p.z = update_one<KIND>(g.z, p.z, s0.z, s1.z, h);
+  p.w = update_one<KIND>(g.w, p.w, s0.w, s1.w, h);
+  *reinterpret_cast<float4*>(s0_ptr) = s0;
+  if (KIND != HVD_KIND_SGD) *reinterpret_cast<float4*>(s1_ptr) = s1;
+  return p;
+}
+
+constexpr int kUnroll = 2;
+
+template <int VARIANT, int KIND>
+__global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedArgs a) {
+  const int rank = hvd_rank(c);
+  const int N = c.nranks;
+  const uint32_t ep = hvd_epoch_load(c, a.slot);
+  // entry barrier: every rank's backward has finished writing this bucket
+  hvd_barrier(c, a.slot, ep + 1, false);
+
+  long long s = a.start, e = a.end;
+  if (VARIANT != HVD_ONESHOT) {
+    long long per = (((a.end - a.start) / 4 + N - 1) / N) * 4;
+    s = a.start + (long long)rank * per;
+    e = s + per < a.end ? s + per : a.end;
+    if (s > e) s = e;
+  }
+  const long long n4 = (e - s) / 4;
+  const long long per_cta = (n4 + gridDim.x - 1) / gridDim.x;
+  const long long i0 = (long long)blockIdx.x * per_cta;
+  const long long i1 = i0 + per_cta < n4 ? i0 + per_cta : n4;
+  float* mine = c.base[rank];
+  float hloc[8];
+  if (KIND != HVD_KIND_NONE) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) hloc[k] = a.hyper[k];
+  }
+
+  for (long long i = i0 + threadIdx.x; i < i1; i += (long long)blockDim.x * kUnroll) {
+    float4 acc[kUnroll];
+    if (VARIANT == HVD_NVLS) {
+#pragma unroll
+      for (int u = 0; u < kUnroll; u++) {
+        const long long idx = i + (long long)u * blockDim.x;
+        if (idx < i1) acc[u] = multimem_ld_reduce_f4(c.mc_base + a.grad_off + s + idx * 4);
+      }
+    } else {
+      float4 v[kUnroll][HVD_MAX_RANKS];
+#pragma unroll
+      for (int u = 0; u < kUnroll; u++) {
+        const long long idx = i + (long long)u * blockDim.x;
+#pragma unroll
+        for (int r = 0; r < HVD_MAX_RANKS; r++)
+          if (r < N && idx < i1) v[u][r] = ld_sys_f4(c.base[r] + a.grad_off + s + idx * 4);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; u++) {
+        acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < HVD_MAX_RANKS; r++)      // fixed order: identical bits on every rank
+          if (r < N) { acc[u].x += v[u][r].x; acc[u].y += v[u][r].y; acc[u].z += v[u][r].z; acc[u].w += v[u][r].w; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; u++) {
+      const long long idx = i + (long long)u * blockDim.x;
+      if (idx >= i1) continue;
+      const long long el = s + idx * 4;
+      float4 g = acc[u];
+      g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
+      float4 res;
+      long long dst_off;
+      if (KIND == HVD_KIND_NONE) { res = g; dst_off = a.out_off + el; }
+      else {
+        res = update_f4<KIND>(g, mine + a.param_off + el, mine + a.slot0_off + el, mine + a.slot1_off + el, hloc);
+        dst_off = a.param_off + el;
+      }
+      if (VARIANT == HVD_ONESHOT) {
+        *reinterpret_cast<float4*>(mine + dst_off) = res;
+      } else if (VARIANT == HVD_TWOSHOT) {
+#pragma unroll
+        for (int r = 0; r < HVD_MAX_RANKS; r++)
+          if (r < N) st_sys_f4(c.base[r] + dst_off, res);
+      } else {
+        multimem_st_f4(c.mc_base + dst_off, res);
+      }
+    }
+  }
+
+  uint32_t next = ep + 1;
+  if (VARIANT != HVD_ONESHOT || a.exit_barrier) {
+    // exit barrier: (two-shot/NVLS) every owner's stores have landed in every arena;
+    // (one-shot) every rank has finished reading my gradients.
+    hvd_barrier(c, a.slot, ep + 2, VARIANT != HVD_ONESHOT);
+    next = ep + 2;
+  }
+  hvd_epoch_store(c, a.slot, next);
+}
+
+// Broadcast [off, off+n) from root's buffer into every rank's buffer (pull over NVLink).
+__global__ void __launch_bounds__(512) hvd_bcast_kernel(HvdCommCtx c, int slot, int root, long long off, long long n) {
+  const int rank = hvd_rank(c);
+  const uint32_t ep = hvd_epoch_load(c, slot);
+  hvd_barrier(c, slot, ep + 1, false);
+  if (rank != root) {
+    const long long n4 = n / 4;
+    const float* src = c.base[root] + off;
+    float* dst = c.base[rank] + off;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x)
+      *reinterpret_cast<float4*>(dst + i * 4) = ld_sys_f4(src + i * 4);
+  }
+  hvd_barrier(c, slot, ep + 2, false);     // root may modify its data again
+  hvd_epoch_store(c, slot, ep + 2);
+}
+
+// ------------------------------------------------------------------------------ launchers
+template <int V, int K>
+static cudaError_t launch_vk(const HvdCommCtx& c, const HvdFusedArgs& a, int ctas, int threads, cudaStream_t st, int emu) {
+  if (emu > 0) {
+    void* args[] = {(void*)&c, (void*)&a};
+    return cudaLaunchCooperativeKernel((void*)hvd_fused_kernel<V, K>, dim3(ctas, emu), dim3(threads), args, 0, st);
+  }
+  hvd_fused_kernel<V, K><<<ctas, threads, 0, st>>>(c, a);
+  return cudaGetLastError();
+}
+
+template <int V>
+static cudaError_t launch_v(const HvdCommCtx& c, const HvdFusedArgs& a, int ctas, int threads, cudaStream_t st, int emu) {
+  switch (a.kind) {
+    case HVD_KIND_NONE: return launch_vk<V, HVD_KIND_NONE>(c, a, ctas, threads, st, emu);
+    case HVD_KIND_SGD: return launch_vk<V, HVD_KIND_SGD>(c, a, ctas, threads, st, emu);
+    case HVD_KIND_ADADELTA: return launch_vk<V, HVD_KIND_ADADELTA>(c, a, ctas, threads, st, emu);
+    case HVD_KIND_ADAM: return launch_vk<V, HVD_KIND_ADAM>(c, a, ctas, threads, st, emu);
+  }
+  return cudaErrorInvalidValue;
+}
+
+static int check_args(const HvdCommCtx* c, const HvdFusedArgs* a, int ctas, int threads) {
+  if (!c || !a || c->nranks < 1 || c->nranks > HVD_MAX_RANKS) return 1;
+  if (ctas < 1 || ctas > HVD_MAX_CTAS || threads < 32 || threads > 256 || threads < c->nranks) return 2;
+  if (a->slot < 0 || a->slot >= HVD_NUM_SLOTS) return 3;
+  if ((a->start | a->end | a->grad_off | a->param_off | a->slot0_off | a->slot1_off | a->out_off) & 3) return 4;
+  if (a->variant == HVD_NVLS && c->mc_base == nullptr) return 5;
+  return 0;
+}
+
+extern "C" int hvd_fused_allreduce_launch(const HvdCommCtx* c, const HvdFusedArgs* a, int ctas, int threads,
+                                          void* stream, int emulate_ranks) {
+  int bad = check_args(c, a, ctas, threads);
+  if (bad) return -bad;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e;
+  switch (a->variant) {
+    case HVD_ONESHOT: e = launch_v<HVD_ONESHOT>(*c, *a, ctas, threads, st, emulate_ranks); break;
+    case HVD_TWOSHOT: e = launch_v<HVD_TWOSHOT>(*c, *a, ctas, threads, st, emulate_ranks); break;
+    case HVD_NVLS: e = launch_v<HVD_NVLS>(*c, *a, ctas, threads, st, emulate_ranks); break;
+    default: return -6;
+  }
+  return (int)e;
+}
+
+extern "C" int hvd_bcast_launch(const HvdCommCtx* c, int slot, int root, long long off, long long n, int ctas,
+                                int threads, void* stream, int emulate_ranks) {
+  if (!c || ctas < 1 || ctas > HVD_MAX_CTAS || threads > 512 || slot < 0 || slot >= HVD_NUM_SLOTS || ((off | n) & 3)) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (emulate_ranks > 0) {
+    void* args[] = {(void*)c, (void*)&slot, (void*)&root, (void*)&off, (void*)&n};
+    return (int)cudaLaunchCooperativeKernel((void*)hvd_bcast_kernel, dim3(ctas, emulate_ranks), dim3(threads), args, 0, st);
+  }
+  hvd_bcast_kernel<<<ctas, threads, 0, st>>>(*c, slot, root, off, n);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int hvd_pad_bytes() { return HVD_NUM_SLOTS * HVD_MAX_CTAS * HVD_MAX_RANKS * (int)sizeof(uint32_t); }
+extern "C" int hvd_epoch_bytes() { return HVD_NUM_SLOTS * HVD_MAX_CTAS * (int)sizeof(uint32_t); }
+
+// ------------------------------------------------------------------------------ runtime helpers
+extern "C" int hvd_cuda_malloc(void** p, long long bytes) { return (int)cudaMalloc(p, (size_t)bytes); }
+extern "C" int hvd_cuda_free(void* p) { return (int)cudaFree(p); }
+extern "C" int hvd_ipc_get_handle(void* p, void* out64) { return (int)cudaIpcGetMemHandle((cudaIpcMemHandle_t*)out64, p); }
+extern "C" int hvd_ipc_open(const void* h64, void** p) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, h64, sizeof(h));
+  return (int)cudaIpcOpenMemHandle(p, h, cudaIpcMemLazyEnablePeerAccess);
+}
+extern "C" int hvd_ipc_close(void* p) { return (int)cudaIpcCloseMemHandle(p); }
+extern "C" int hvd_can_access_peer(int dev, int peer) {
+  int ok = 0;
+  if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) return -1;
+  return ok;
+}
+extern "C" const char* hvd_cuda_error_string(int e) { return cudaGetErrorString((cudaError_t)e); }

@@ -117,11 +117,11 @@ class Model:
         from .. import basics
         allocator = None
         double = False
-        if device.type == "cuda" and basics.is_initialized() and basics.size() > 1:
+        if device.type == "cuda" and basics.is_initialized():
             from ..parallel import peer
             if peer.available():
                 allocator = peer.context().alloc_tensor
-                double = True        # double-buffered grads drop the exit barrier
+                double = basics.size() > 1   # double-buffered grads drop the exit barrier
         self.arena = ParamArena(specs, device, n_slots, double_grads=double, allocator=allocator)
         g = torch.Generator().manual_seed(self._seed) if self._seed is not None else None
         with torch.no_grad():

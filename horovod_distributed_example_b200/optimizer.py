@@ -47,8 +47,8 @@ class _DistributedMixin:
         self._buckets = bucket_mod.plan(arena, thr, self._cut_after)
         self._plan_hash = bucket_mod.check_agreement(arena, self._buckets)
         self._fused = None
-        if basics.is_initialized() and basics.size() > 1 and arena.device.type == "cuda" \
-                and arena.symmetric:
+        if basics.is_initialized() and arena.device.type == "cuda" and arena.symmetric \
+                and self.kind != 0:
             from .parallel import fused
             self._fused = fused.FusedReducer(arena, self, self._buckets)
 
@@ -77,6 +77,11 @@ class _DistributedMixin:
                 seg.copy_(self._compression.decompress(comp, ctx))
         return g
 
+    def materialize_state(self) -> None:
+        """Gather sharded optimizer slots to this rank (before a checkpoint is written)."""
+        if self._fused is not None:
+            self._fused.materialize_state()
+
     def begin_step(self) -> None:
         basics.state().step += 1
 
@@ -90,8 +95,21 @@ class _DistributedMixin:
             self.iterations += 1
             self._fused.run_all()
             self._push_hyper()
+            cfg = basics.config()
+            if cfg.debug_checksum and self.iterations % cfg.debug_checksum == 0:
+                self._check_replicas(arena)
             return
         super().apply_gradients(arena)
+
+
+def _check_replicas_impl(arena):
+    cs = int(arena.checksum())
+    all_cs = collectives.allgather_object(cs)
+    if any(c != all_cs[0] for c in all_cs):
+        raise RuntimeError(f"replica divergence detected (HVD_DEBUG_CHECKSUM): checksums {all_cs}")
+
+
+_DistributedMixin._check_replicas = staticmethod(_check_replicas_impl)
 
 
 def DistributedOptimizer(optimizer, name=None, device_dense="", device_sparse="",

@@ -1,0 +1,98 @@
+"""Per-bucket fused allreduce + 1/N scale + optimizer update over the symmetric arena.
+
+This is what ``hvd.DistributedOptimizer`` runs on B200 instead of "allreduce, then update"
+(reference ``mnist_keras.py:87``; Horovod path in SURVEY.md section 3.2).  One kernel launch
+per bucket (``csrc/comm/fused_allreduce.cu``); the variant (one-shot / two-shot / NVLS) is
+fixed per bucket at construction from the variant table, because two-shot/NVLS buckets keep
+their optimizer state *sharded* by owner rank and must not change owner mid-training.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from .. import basics
+from . import peer as peer_mod
+from .peer import HvdFusedArgs, NVLS, ONESHOT, TWOSHOT, VARIANT_NAMES
+
+
+class FusedReducer:
+    def __init__(self, arena, optimizer, buckets, ctx: Optional[peer_mod.PeerContext] = None,
+                 variants: Optional[List[int]] = None):
+        self.arena, self.opt, self.buckets = arena, optimizer, list(buckets)
+        self.ctx = ctx or peer_mod.context()
+        buf, off = self.ctx.buffer_of(arena.buffer)
+        if buf is None:
+            raise RuntimeError("the arena does not live in symmetric memory")
+        self.buf, self.base_off = buf, off
+        if len(self.buckets) > peer_mod.NUM_SLOTS - 4:
+            raise RuntimeError("too many buckets for the signal pad; raise HVD_FUSION_THRESHOLD")
+        cfg = basics.state().config
+        forced = cfg.allreduce_variant if cfg else "auto"
+        from . import variants as vt
+        self.variants, self.ctas = [], []
+        for i, b in enumerate(self.buckets):
+            v, c = vt.pick(b.nbytes, self.ctx.size, bool(buf.mc_ptr), forced, cfg.comm_ctas if cfg else 0)
+            if variants is not None:
+                v = variants[i]
+            self.variants.append(v)
+            self.ctas.append(c)
+        self.side_stream = torch.cuda.Stream(device=arena.device)
+        self._events = [torch.cuda.Event() for _ in self.buckets]
+
+    def describe(self) -> List[str]:
+        return [f"bucket{b.index}[{b.start}:{b.end}] {b.nbytes}B {VARIANT_NAMES[v]} ctas={c}"
+                for b, v, c in zip(self.buckets, self.variants, self.ctas)]
+
+    def _args(self, i: int, grad_buf: int, exit_barrier: int) -> HvdFusedArgs:
+        b, ar = self.buckets[i], self.arena
+        a = HvdFusedArgs()
+        a.start, a.end = b.start, b.end
+        a.grad_off = self.base_off + ar.grad_offset(grad_buf)
+        a.param_off = self.base_off + ar.param_offset
+        a.slot0_off = self.base_off + (ar.slot_offset(0) if ar.n_slots > 0 else 0)
+        a.slot1_off = self.base_off + (ar.slot_offset(1) if ar.n_slots > 1 else 0)
+        a.out_off = a.grad_off
+        a.hyper = self.opt.hyper.data_ptr()
+        a.scale = 1.0 / self.ctx.size
+        a.kind, a.variant, a.slot, a.exit_barrier = self.opt.kind, self.variants[i], i, exit_barrier
+        return a
+
+    def run_bucket(self, i: int, grad_buf: int = 0, exit_barrier: int = 1, stream=None) -> None:
+        self.ctx.launch_fused(self.buf, self._args(i, grad_buf, exit_barrier), self.ctas[i], stream=stream)
+
+    def run_all(self, grad_buf: int = 0, exit_barrier: int = 1, stream=None) -> None:
+        tl = basics.state().timeline
+        for i in range(len(self.buckets)):
+            if tl is not None:
+                tl.begin(f"grad.bucket{i}", "FUSED_ALLREDUCE_UPDATE")
+            self.run_bucket(i, grad_buf, exit_barrier, stream)
+            if tl is not None:
+                tl.end(f"grad.bucket{i}", "FUSED_ALLREDUCE_UPDATE")
+
+    def shard_range(self, i: int, rank: int):
+        b, n = self.buckets[i], self.ctx.size
+        per = (((b.end - b.start) // 4 + n - 1) // n) * 4
+        s = min(b.start + rank * per, b.end)
+        return s, min(s + per, b.end)
+
+    def materialize_state(self) -> None:
+        """Pull the optimizer-slot shards owned by other ranks into this rank's arena (one-sided
+        peer reads; called by rank 0 before it writes a checkpoint)."""
+        ar = self.arena
+        torch.cuda.synchronize(ar.device)
+        for i, v in enumerate(self.variants):
+            if v == ONESHOT:
+                continue
+            for r in range(self.ctx.size):
+                if r == (0 if self.ctx.emulated else self.ctx.rank):
+                    continue
+                s, e = self.shard_range(i, r)
+                if e <= s:
+                    continue
+                remote = self.buf.peer_tensor(r)
+                for k in range(ar.n_slots):
+                    o = self.base_off + ar.slot_offset(k)
+                    self.buf.tensor[o + s:o + e].copy_(remote[o + s:o + e])
+        torch.cuda.synchronize(ar.device)

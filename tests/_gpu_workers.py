@@ -1,0 +1,87 @@
+"""Bodies for the real multi-GPU tests (one process per GPU, launched by hvdrun)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+import horovod_distributed_example_b200 as hvd
+from horovod_distributed_example_b200 import keras
+
+
+def collectives():
+    hvd.init()
+    r, n = hvd.rank(), hvd.size()
+    from horovod_distributed_example_b200.parallel import peer
+    ctx = peer.context()
+    print(f"rank {r}: backend={ctx.backend} multicast={ctx.multicast}", flush=True)
+    for forced in ("oneshot", "twoshot", "nvls"):
+        hvd.basics.state().config.allreduce_variant = forced
+        for numel in (1, 7, 1000, 300000, 3 << 20):
+            t = torch.full((numel,), float(r + 1), device="cuda") + torch.arange(numel, device="cuda") % 5
+            exp = (torch.arange(numel, device="cuda") % 5).float() + (n + 1) / 2
+            out = hvd.allreduce(t, average=True)
+            torch.testing.assert_close(out, exp, rtol=1e-6, atol=1e-6)
+    hvd.basics.state().config.allreduce_variant = "auto"
+    b = hvd.broadcast(torch.arange(1000.0, device="cuda") * (r + 1), root_rank=n - 1)
+    assert torch.equal(b, torch.arange(1000.0, device="cuda") * n)
+    torch.cuda.synchronize()
+    ctx.check_error()
+    print("OK", flush=True)
+
+
+def train_replicas():
+    """MNIST CNN data-parallel: ranks start identical after the broadcast, stay bit-identical
+    after every fused step, and match a single-process run on the concatenated batch."""
+    hvd.init()
+    r, n = hvd.rank(), hvd.size()
+    os.environ["HVD_DEBUG_CHECKSUM"] = "1"
+    hvd.basics.state().config.debug_checksum = 1
+    m = keras.Sequential([
+        keras.layers.Conv2D(32, (3, 3), activation='relu', input_shape=(28, 28, 1)),
+        keras.layers.Conv2D(64, (3, 3), activation='relu'),
+        keras.layers.MaxPooling2D((2, 2)), keras.layers.Flatten(),
+        keras.layers.Dense(128, activation='relu'), keras.layers.Dense(10, activation='softmax')], seed=10 + r)
+    opt = hvd.DistributedOptimizer(keras.optimizers.Adadelta(1.0 * n))
+    m.compile(loss=keras.losses.SparseCategoricalCrossentropy(), optimizer=opt, metrics=['accuracy'])
+    rng = np.random.default_rng(3)
+    X = rng.random((n * 32, 28, 28, 1), dtype=np.float32)
+    Y = rng.integers(0, 10, n * 32)
+    m._ensure_built((32, 28, 28, 1))
+    assert m.arena.symmetric and opt._fused is not None, "fused peer path not active"
+    cb = hvd.callbacks.BroadcastGlobalVariablesCallback(0)
+    cb.set_model(m)
+    cb.on_train_begin()
+    w0 = m.arena.params.clone()
+    # oracle: one process, the whole batch, same init
+    ref = keras.Sequential.from_config(m.get_config())
+    import horovod_distributed_example_b200.keras.models as mm
+    ref.build((28, 28, 1))
+    ref.compile(loss=keras.losses.SparseCategoricalCrossentropy(), optimizer=keras.optimizers.Adadelta(1.0 * n))
+    ref._ensure_built((32, 28, 28, 1))
+    ref.set_weights(m.get_weights())
+    for step in range(3):
+        m.train_on_batch(X[r * 32:(r + 1) * 32], Y[r * 32:(r + 1) * 32])
+        ref.train_on_batch(X, Y)
+    torch.cuda.synchronize()
+    cs = hvd.allgather_object(int(m.arena.checksum()))
+    assert all(c == cs[0] for c in cs), cs
+    got = torch.cat([torch.from_numpy(w).reshape(-1) for w in m.get_weights()])
+    exp = torch.cat([torch.from_numpy(w).reshape(-1) for w in ref.get_weights()])
+    torch.testing.assert_close(got, exp, rtol=2e-3, atol=2e-4)
+    assert not torch.equal(m.arena.params, w0)
+    if r == 0:
+        import tempfile
+        d = tempfile.mkdtemp()
+        m.save(os.path.join(d, "checkpoint-1.h5"))
+        m2 = keras.load_model(os.path.join(d, "checkpoint-1.h5"))
+        np.testing.assert_array_equal(m2.get_weights()[0], m.get_weights()[0])
+    hvd.barrier()
+    print("OK", flush=True)
+
+
+if __name__ == "__main__":
+    globals()[os.environ["HVD_TEST_BODY"]]()
