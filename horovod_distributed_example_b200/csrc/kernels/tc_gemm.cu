@@ -1,0 +1,198 @@
+// Generic tcgen05 TF32 GEMM:  D[M,N] (fp32, row-major) (+)= A * B,  M tile 128, N tile 64/128, K block 32.
+//
+// Operands come straight from row-major global tensors through TMA, in either major-ness:
+//   A "K-major"  : tensor [M][K]   (rows of K contiguous)      A "MN-major": tensor [K][M]
+//   B "K-major"  : tensor [N][K]                                B "MN-major": tensor [K][N]
+// so the four combinations cover  X*W, X*W^T, X^T*dY, ...  without any transpose kernels - the
+// dense-layer forward (x[B,9216] * W[9216,128]: A K-major, B MN-major), dgrad (dY * W^T: A K-major,
+// B K-major) and wgrad (X^T * dY: A MN-major, B MN-major) of the reference's Dense(128) layer
+// (mnist_keras.py:79) are all this kernel.
+//
+// Structure (one CTA per output tile or per split-K slice, 256 threads):
+//   warp 0 : TMA producer          (one elected lane; 4-stage smem ring, mbarrier full/empty)
+//   warp 1 : MMA issuer            (one elected lane; tcgen05.mma kind::tf32, accumulator in TMEM)
+//   warp 2 : TMEM allocator
+//   warps 4-7 : epilogue           (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 32;          // 32 fp32 = 128 B = one swizzle row
+constexpr int STAGES = 4;
+
+enum Epilogue { EPI_STORE = 0, EPI_ATOMIC_ADD = 1, EPI_BIAS_RELU = 2 };
+
+struct GemmParams {
+  int M, N, K;
+  int k_split;                   // gridDim.z slices of K
+  float* D;
+  long long ldd;
+  const float* bias;
+  int epilogue;
+  uint32_t lbo_a, sbo_a, lbo_b, sbo_b;   // 0 = default (test hook for descriptor bring-up)
+};
+
+template <int BN>
+struct Smem {
+  static constexpr int A_BYTES = BM * BK * 4;     // 16 KB
+  static constexpr int B_BYTES = BN * BK * 4;
+  static constexpr int STAGE = A_BYTES + B_BYTES;
+  static constexpr int TOTAL = STAGES * STAGE + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(256, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Smem<BN>::STAGE);
+  uint64_t* full = bars;                 // [STAGES]
+  uint64_t* empty = bars + STAGES;       // [STAGES]
+  uint64_t* acc_full = bars + 2 * STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  const int kb_total = p.K / BK;
+  const int kb_per = (kb_total + p.k_split - 1) / p.k_split;
+  const int kb_begin = blockIdx.z * kb_per;
+  const int kb_end = min(kb_total, kb_begin + kb_per);
+  const int nkb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    tc::tma_prefetch_desc(&tmA);
+    tc::tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
+    tc::mbar_init(acc_full, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 2) tc::tmem_alloc<BN>(tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (tc::elect_one()) {
+      for (int i = 0; i < nkb; i++) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        tc::mbar_wait(&empty[s], ph ^ 1);
+        uint8_t* a = smem + s * Smem<BN>::STAGE;
+        uint8_t* b = a + Smem<BN>::A_BYTES;
+        tc::mbar_expect_tx(&full[s], Smem<BN>::STAGE);
+        const int k0 = (kb_begin + i) * BK;
+        if (!A_MN) tc::tma_load_2d(a, &tmA, &full[s], k0, m0);
+        else
+          for (int j = 0; j < BM / 32; j++) tc::tma_load_2d(a + j * (BK * 128), &tmA, &full[s], m0 + 32 * j, k0);
+        if (!B_MN) tc::tma_load_2d(b, &tmB, &full[s], k0, n0);
+        else
+          for (int j = 0; j < BN / 32; j++) tc::tma_load_2d(b + j * (BK * 128), &tmB, &full[s], n0 + 32 * j, k0);
+      }
+    }
+  } else if (warp == 1) {
+    if (tc::elect_one()) {
+      constexpr uint32_t idesc = tc::make_idesc_tf32(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      const uint32_t lbo_a = p.lbo_a ? p.lbo_a : (A_MN ? BK * 128 : 16), sbo_a = p.sbo_a ? p.sbo_a : (A_MN ? 512 : 1024);
+      const uint32_t lbo_b = p.lbo_b ? p.lbo_b : (B_MN ? BK * 128 : 16), sbo_b = p.sbo_b ? p.sbo_b : (B_MN ? 512 : 1024);
+      for (int i = 0; i < nkb; i++) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        tc::mbar_wait(&full[s], ph);
+        tc::tc_fence_after();
+        const uint32_t a = tc::smem_u32(smem + s * Smem<BN>::STAGE);
+        const uint32_t b = a + Smem<BN>::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / 8; k++) {        // UMMA_K = 8 for tf32
+          const uint64_t da = tc::make_smem_desc(a + (A_MN ? k * 1024 : k * 32), lbo_a, sbo_a, A_MN ? 1 : 2);
+          const uint64_t db = tc::make_smem_desc(b + (B_MN ? k * 1024 : k * 32), lbo_b, sbo_b, B_MN ? 1 : 2);
+          tc::mma_tf32(tmem, da, db, idesc, (i | k) != 0);
+        }
+        tc::mma_commit(&empty[s]);                // frees the smem stage when these MMAs retire
+      }
+      tc::mma_commit(acc_full);
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3;                       // TMEM lane quadrant this warp may read
+    tc::mbar_wait(acc_full, 0);
+    tc::tc_fence_after();
+    const int row = m0 + q * 32 + lane;
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 32) {
+      float v[32];
+      tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + c, v);
+      tc::tmem_ld_wait();
+      if (nkb <= 0) {
+#pragma unroll
+        for (int j = 0; j < 32; j++) v[j] = 0.f;
+      }
+      if (row < p.M) {
+        float* d = p.D + (long long)row * p.ldd + n0 + c;
+        if (p.epilogue == EPI_ATOMIC_ADD) {
+#pragma unroll
+          for (int j = 0; j < 32; j++) if (n0 + c + j < p.N) atomicAdd(d + j, v[j]);
+        } else {
+          if (p.epilogue == EPI_BIAS_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; j++) v[j] = fmaxf(v[j] + p.bias[n0 + c + j], 0.f);
+          }
+          if (n0 + c + 32 <= p.N) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(d + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            for (int j = 0; j < 32; j++) if (n0 + c + j < p.N) d[j] = v[j];
+          }
+        }
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc<BN>(tmem);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+  auto k = tc_gemm_kernel<BN, A_MN, B_MN>;
+  static bool attr = false;
+  if (!attr) {
+    if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<BN>::TOTAL) != cudaSuccess) return -10;
+    attr = true;
+  }
+  dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN, p.k_split);
+  k<<<grid, 256, Smem<BN>::TOTAL, st>>>(ta, tb, p);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace
+
+// A: [M][K] (a_mn=0) or [K][M] (a_mn=1); B: [N][K] (b_mn=0) or [K][N] (b_mn=1); all dense row-major fp32.
+// K must be a multiple of 32; M/N tails are zero-filled by TMA and masked in the epilogue.
+extern "C" int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int bn,
+                           int k_split, int epilogue, const float* bias, long long ldd, void* stream,
+                           unsigned lbo_a, unsigned sbo_a, unsigned lbo_b, unsigned sbo_b) {
+  if (K % BK != 0 || (bn != 64 && bn != 128) || k_split < 1) return -1;
+  CUtensorMap ta, tb;
+  {
+    uint64_t dims[2], str[1];
+    uint32_t box[2];
+    if (!a_mn) { dims[0] = K; dims[1] = M; str[0] = (uint64_t)K * 4; box[0] = BK; box[1] = BM; }
+    else { dims[0] = M; dims[1] = K; str[0] = (uint64_t)M * 4; box[0] = 32; box[1] = BK; }
+    if (tc::make_tmap(&ta, A, 2, dims, str, box, a_mn != 0)) return -2;
+    if (!b_mn) { dims[0] = K; dims[1] = N; str[0] = (uint64_t)K * 4; box[0] = BK; box[1] = (uint32_t)bn; }
+    else { dims[0] = N; dims[1] = K; str[0] = (uint64_t)N * 4; box[0] = 32; box[1] = BK; }
+    if (tc::make_tmap(&tb, B, 2, dims, str, box, b_mn != 0)) return -3;
+  }
+  GemmParams p{M, N, K, k_split, D, ldd ? ldd : (long long)N, bias, epilogue, lbo_a, sbo_a, lbo_b, sbo_b};
+  cudaStream_t st = (cudaStream_t)stream;
+#define HVD_CASE(BN_, AM, BMN) if (bn == BN_ && a_mn == AM && b_mn == BMN) return launch<BN_, AM != 0, BMN != 0>(ta, tb, p, st);
+  HVD_CASE(64, 0, 0) HVD_CASE(64, 0, 1) HVD_CASE(64, 1, 0) HVD_CASE(64, 1, 1)
+  HVD_CASE(128, 0, 0) HVD_CASE(128, 0, 1) HVD_CASE(128, 1, 0) HVD_CASE(128, 1, 1)
+#undef HVD_CASE
+  return -4;
+}

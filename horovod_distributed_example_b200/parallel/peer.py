@@ -156,8 +156,9 @@ class _FdExchange:
         return os.path.join(self.dir, f"r{r}.sock")
 
     def send(self, dst: int, fd: int, tag: int):
-        socket.send_fds(self.sock, [tag.to_bytes(4, "little") + self.rank.to_bytes(4, "little")], [fd],
-                        address=self._peer(dst))
+        # socket.send_fds() drops its `address` argument on this Python; call sendmsg directly
+        self.sock.sendmsg([tag.to_bytes(4, "little") + self.rank.to_bytes(4, "little")],
+                          [(socket.SOL_SOCKET, socket.SCM_RIGHTS, array.array("i", [fd]))], 0, self._peer(dst))
 
     def recv(self):
         msg, fds, _flags, _addr = socket.recv_fds(self.sock, 8, 1)
@@ -450,7 +451,7 @@ class PeerContext:
                 and t.numel() % 4 == 0:
             self._allreduce_range(buf, off, t.numel(), average)
             return t
-        cap = self.staging_bytes // 4
+        cap = self.staging_bytes // 8            # first half: inputs, second half: results
         src = t.reshape(-1).to(torch.float32) if (t.dtype != torch.float32 or not t.is_contiguous()) \
             else t.reshape(-1)
         n = src.numel()
@@ -462,19 +463,25 @@ class PeerContext:
             stage[:m].copy_(src[s:s + m])
             if m4 > m:
                 stage[m:m4].zero_()
-            self._allreduce_range(self.staging, 0, m4, average)
-            out[s:s + m].copy_(stage[:m])
+            self._allreduce_range(self.staging, 0, m4, average, out_off=cap)
+            out[s:s + m].copy_(stage[cap:cap + m])
         if out.data_ptr() != t.data_ptr():
             t.copy_(out.view(t.shape).to(t.dtype))
         return t
 
-    def _allreduce_range(self, buf: SymmBuffer, off: int, n: int, average: bool, stream=None):
+    def _allreduce_range(self, buf: SymmBuffer, off: int, n: int, average: bool, stream=None,
+                         out_off: Optional[int] = None):
         variant, ctas = self._pick(n * 4)
         if variant == NVLS and not buf.mc_ptr:
             variant = TWOSHOT
+        if out_off is None and variant == ONESHOT:
+            # in place: a one-shot rank would overwrite data its peers are still reading;
+            # two-shot is safe in place (each element is read only by its single owner CTA)
+            variant = TWOSHOT
         a = HvdFusedArgs()
         a.start, a.end = 0, n
-        a.grad_off = a.out_off = off
+        a.grad_off = off
+        a.out_off = off if out_off is None else out_off
         a.param_off = a.slot0_off = a.slot1_off = 0
         a.hyper = None
         a.scale = 1.0 / self.size if average else 1.0

@@ -48,7 +48,7 @@ def test_emulated_allreduce_matches_sum(ctx4, variant, n):
         buf.peer_tensor(r)[:n4].copy_(vals[r])
     a = P.HvdFusedArgs()
     a.start, a.end = 0, n4
-    a.grad_off = a.out_off = 0
+    a.grad_off, a.out_off = 0, (0 if variant else 1 << 20)   # one-shot must not run in place
     a.scale, a.kind, a.variant, a.slot, a.exit_barrier = 1.0 / ctx.size, 0, variant, P.SLOT_STAGING, 1
     for _ in range(3):                      # repeated launches exercise the monotonic epochs
         for r in range(ctx.size):
@@ -60,7 +60,8 @@ def test_emulated_allreduce_matches_sum(ctx4, variant, n):
     for r in range(1, ctx.size):
         ref += vals[r]                       # same fixed order as the kernel
     ref *= 1.0 / ctx.size
-    outs = [buf.peer_tensor(r)[:n4].clone() for r in range(ctx.size)]
+    oo = a.out_off
+    outs = [buf.peer_tensor(r)[oo:oo + n4].clone() for r in range(ctx.size)]
     for o in outs:
         assert torch.equal(o, outs[0])       # bit-identical on every rank
     torch.testing.assert_close(outs[0], ref, rtol=1e-6, atol=1e-6)
