@@ -21,7 +21,11 @@ constexpr int BM = 128;
 constexpr int BK = 32;          // 32 fp32 = 128 B = one swizzle row
 constexpr int STAGES = 4;
 
-enum Epilogue { EPI_STORE = 0, EPI_ATOMIC_ADD = 1, EPI_BIAS_RELU = 2 };
+// EPI_UNPOOL: D is the conv2 output gradient [B,24,24,64]; the GEMM result (gradient wrt the pooled,
+// dropped-out activations, row = sample, column = flat (ph,pw,c)) is routed through the mask byte
+// written by conv2_fprop: scaled by 1/keep where live, placed at the arg-max of its 2x2 window,
+// zeros at the other three positions - MaxPool/Dropout/ReLU backward fused into the dgrad epilogue.
+enum Epilogue { EPI_STORE = 0, EPI_ATOMIC_ADD = 1, EPI_BIAS_RELU = 2, EPI_UNPOOL = 3 };
 
 struct GemmParams {
   int M, N, K;
@@ -31,6 +35,8 @@ struct GemmParams {
   const float* bias;
   int epilogue;
   uint32_t lbo_a, sbo_a, lbo_b, sbo_b;   // 0 = default (test hook for descriptor bring-up)
+  const uint8_t* mask;                   // EPI_UNPOOL
+  float scale;                           // EPI_UNPOOL: 1/keep
 };
 
 template <int BN>
@@ -56,7 +62,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM;
   const int n0 = blockIdx.y * BN;
-  const int kb_total = p.K / BK;
+  const int kb_total = (p.K + BK - 1) / BK;      // a K tail is zero-filled by TMA
   const int kb_per = (kb_total + p.k_split - 1) / p.k_split;
   const int kb_begin = blockIdx.z * kb_per;
   const int kb_end = min(kb_total, kb_begin + kb_per);
@@ -131,7 +137,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int j = 0; j < 32; j++) v[j] = 0.f;
       }
-      if (row < p.M) {
+      if (row < p.M && p.epilogue == EPI_UNPOOL) {
+        const int f = n0 + c;                                  // flat (ph, pw, c0) with c0 in {0, 32}
+        const int ph = f / (12 * 64), pw = (f / 64) % 12, c0 = f & 63;
+        const uint4* mp = reinterpret_cast<const uint4*>(p.mask + (long long)row * 9216 + f);
+        const uint4 m0 = mp[0], m1 = mp[1];
+        const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+        float* base = p.D + (((long long)row * 24 + 2 * ph) * 24 + 2 * pw) * 64 + c0;
+#pragma unroll
+        for (int pos = 0; pos < 4; pos++) {
+          float* d = base + ((pos >> 1) * 24 + (pos & 1)) * 64;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float o[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              const uint32_t mb = (mw[(j + e) >> 2] >> (8 * ((j + e) & 3))) & 0xff;
+              o[e] = ((mb & 4) && (int)(mb & 3) == pos) ? v[j + e] * p.scale : 0.f;
+            }
+            *reinterpret_cast<float4*>(d + j) = make_float4(o[0], o[1], o[2], o[3]);
+          }
+        }
+      } else if (row < p.M) {
         float* d = p.D + (long long)row * p.ldd + n0 + c;
         if (p.epilogue == EPI_ATOMIC_ADD) {
 #pragma unroll
@@ -172,11 +199,12 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cu
 }  // namespace
 
 // A: [M][K] (a_mn=0) or [K][M] (a_mn=1); B: [N][K] (b_mn=0) or [K][N] (b_mn=1); all dense row-major fp32.
-// K must be a multiple of 32; M/N tails are zero-filled by TMA and masked in the epilogue.
+// M/N/K tails are zero-filled by TMA (out-of-bounds box elements) and masked in the epilogue.
 extern "C" int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int bn,
                            int k_split, int epilogue, const float* bias, long long ldd, void* stream,
-                           unsigned lbo_a, unsigned sbo_a, unsigned lbo_b, unsigned sbo_b) {
-  if (K % BK != 0 || (bn != 64 && bn != 128) || k_split < 1) return -1;
+                           unsigned lbo_a, unsigned sbo_a, unsigned lbo_b, unsigned sbo_b, const uint8_t* mask,
+                           float scale) {
+  if ((bn != 64 && bn != 128) || k_split < 1 || K < 1) return -1;
   CUtensorMap ta, tb;
   {
     uint64_t dims[2], str[1];
@@ -188,7 +216,7 @@ extern "C" int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int 
     else { dims[0] = N; dims[1] = K; str[0] = (uint64_t)N * 4; box[0] = 32; box[1] = BK; }
     if (tc::make_tmap(&tb, B, 2, dims, str, box, b_mn != 0)) return -3;
   }
-  GemmParams p{M, N, K, k_split, D, ldd ? ldd : (long long)N, bias, epilogue, lbo_a, sbo_a, lbo_b, sbo_b};
+  GemmParams p{M, N, K, k_split, D, ldd ? ldd : (long long)N, bias, epilogue, lbo_a, sbo_a, lbo_b, sbo_b, mask, scale};
   cudaStream_t st = (cudaStream_t)stream;
 #define HVD_CASE(BN_, AM, BMN) if (bn == BN_ && a_mn == AM && b_mn == BMN) return launch<BN_, AM != 0, BMN != 0>(ta, tb, p, st);
   HVD_CASE(64, 0, 0) HVD_CASE(64, 0, 1) HVD_CASE(64, 1, 0) HVD_CASE(64, 1, 1)

@@ -7,7 +7,7 @@ import torch
 
 from . import native
 
-EPI_STORE, EPI_ATOMIC_ADD, EPI_BIAS_RELU = 0, 1, 2
+EPI_STORE, EPI_ATOMIC_ADD, EPI_BIAS_RELU, EPI_UNPOOL = 0, 1, 2, 3
 
 
 def _lib():
@@ -17,14 +17,16 @@ def _lib():
         lib.hvd_tc_gemm.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_int, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p,
-                                    ctypes.c_uint, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint]
+                                    ctypes.c_uint, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint,
+                                    ctypes.c_void_p, ctypes.c_float]
         lib._hvd_gemm_declared = True
     return lib
 
 
 def tc_gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn: bool = False, b_mn: bool = False,
             bn: int = 128, k_split: int = 1, epilogue: int = EPI_STORE, bias: torch.Tensor = None,
-            out: torch.Tensor = None, dbg=(0, 0, 0, 0)) -> torch.Tensor:
+            out: torch.Tensor = None, dbg=(0, 0, 0, 0), mask: torch.Tensor = None, scale: float = 1.0,
+            stream=None) -> torch.Tensor:
     """D[M,N] = A*B on the tensor cores (TF32 in, fp32 accumulate).
 
     ``A`` is ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``B`` is ``[N,K]`` or ``[K,N]``.
@@ -36,7 +38,8 @@ def tc_gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn: bool
             else torch.empty(M, N, device=A.device, dtype=torch.float32)
     rc = _lib().hvd_tc_gemm(A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, int(a_mn), int(b_mn), bn, k_split,
                             epilogue, bias.data_ptr() if bias is not None else None, out.stride(0),
-                            torch.cuda.current_stream().cuda_stream, *dbg)
+                            stream if stream is not None else torch.cuda.current_stream().cuda_stream, *dbg,
+                            mask.data_ptr() if mask is not None else None, float(scale))
     if rc != 0:
         raise RuntimeError(f"hvd_tc_gemm failed: {rc}")
     return out
