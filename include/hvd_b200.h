@@ -1,0 +1,130 @@
+/* hvd_b200.h - C ABI of the native libraries (bound from Python with ctypes; usable from C/C++).
+ *
+ *   libhvd_core.so  host runtime   (g++; CUDA driver resolved with dlopen, loads on CPU-only hosts)
+ *   libhvd_cuda.so  sm_100a kernels (nvcc -gencode arch=compute_100a,code=sm_100a)
+ *
+ * Every function returns 0 on success unless noted.  Device pointers are raw addresses; `stream`
+ * is a cudaStream_t.  The reference (weikaolun/horovod-distributed-example) has no native code of
+ * its own: each block cites the script line / Horovod component whose capability it provides.
+ */
+#ifndef HVD_B200_H_
+#define HVD_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ libhvd_core.so */
+
+/* Static bucket plan - replaces Horovod's per-cycle tensor fusion (controller.cc, fusion_buffer_manager.cc)
+ * behind hvd.DistributedOptimizer (reference mnist_keras.py:87).  out: 4 int64 per bucket
+ * (start, end, first_tensor, last_tensor).  Returns the bucket count. */
+int64_t hvd_plan_buckets(const int64_t* offsets, const int64_t* numels, int64_t n, int64_t slab_elems,
+                         int64_t threshold_bytes, const int64_t* cuts, int64_t n_cuts, int64_t* out);
+uint64_t hvd_fnv1a(uint64_t h, const uint8_t* data, int64_t n);
+uint32_t hvd_crc32c(const uint8_t* p, int64_t n);
+
+/* TF event files - what keras.callbacks.TensorBoard writes (reference mnist_keras.py:105). */
+void* hvd_ev_open(const char* path);
+int hvd_ev_scalar(void* h, const char* tag, double value, int64_t step, double wall_time);
+void hvd_ev_flush(void* h);
+void hvd_ev_close(void* h);
+
+/* Chrome-trace timeline - HOROVOD_TIMELINE (Horovod timeline.cc). ph: 'B','E','i','X'. */
+void* hvd_tl_open(const char* path);
+int hvd_tl_event(void* h, const char* tensor, const char* activity, char ph, int64_t ts_us, int64_t dur_us);
+int64_t hvd_tl_now_us(void* h);
+void hvd_tl_close(void* h);
+
+/* Minimal HDF5 writer/reader - the checkpoint-{epoch}.h5 files of ModelCheckpoint / model.save /
+ * load_model (reference mnist_keras.py:101-104,118-119,124).  dtype: 0 f32, 1 i64, 2 f64, 3 i32, 4 string. */
+const char* hvd_h5_last_error(void);
+void* hvd_h5w_create(void);
+void hvd_h5w_free(void* w);
+int hvd_h5w_group(void* w, const char* path);
+int hvd_h5w_dataset(void* w, const char* path, int dtype, int rank, const int64_t* dims, const void* data);
+int hvd_h5w_attr_str(void* w, const char* obj, const char* name, const char* data, int64_t len);
+int hvd_h5w_attr_strs(void* w, const char* obj, const char* name, const char* packed, int64_t n, int64_t width);
+int hvd_h5w_attr_num(void* w, const char* obj, const char* name, int dtype, int rank, const int64_t* dims, const void* data);
+int hvd_h5w_write(void* w, const char* filename);
+void* hvd_h5r_open(const char* filename);
+void hvd_h5r_close(void* r);
+int hvd_h5r_kind(void* r, const char* path); /* 0 missing, 1 group, 2 dataset */
+int64_t hvd_h5r_list(void* r, const char* path, char* out, int64_t cap);
+int hvd_h5r_dataset_info(void* r, const char* path, int* dtype, int* rank, int64_t* dims, int64_t* elsize);
+int hvd_h5r_dataset_read(void* r, const char* path, void* out, int64_t nbytes);
+int64_t hvd_h5r_attr_list(void* r, const char* obj, char* out, int64_t cap);
+int hvd_h5r_attr_info(void* r, const char* obj, const char* name, int* dtype, int* rank, int64_t* dims, int64_t* elsize);
+int hvd_h5r_attr_read(void* r, const char* obj, const char* name, void* out, int64_t nbytes);
+
+/* Symmetric (peer-mapped) memory on the CUDA VMM driver API - the exportable replacement of Horovod's
+ * fusion buffer; communicator setup behind hvd.init() (reference mnist_keras.py:30). */
+const char* hvd_symm_last_error(void);
+int hvd_symm_available(void);
+int hvd_symm_multicast_supported(int device);
+int hvd_symm_handle_type_supported(int device);
+long long hvd_symm_round_size(int device, long long bytes, int nranks_for_multicast);
+int hvd_symm_create(int device, long long bytes, unsigned long long* handle, int* fd);
+int hvd_symm_import(int fd, unsigned long long* handle);
+int hvd_symm_map(int device, unsigned long long handle, long long bytes, unsigned long long* ptr);
+int hvd_symm_unmap(unsigned long long ptr, long long bytes);
+int hvd_symm_release(unsigned long long handle);
+int hvd_symm_mc_create(int ndev, long long bytes, unsigned long long* mc, int* fd);
+int hvd_symm_mc_add_device(unsigned long long mc, int device);
+int hvd_symm_mc_bind(unsigned long long mc, unsigned long long mem, long long bytes);
+
+/* ------------------------------------------------------------------ libhvd_cuda.so */
+
+struct HvdCommCtx;   /* csrc/comm/comm.cuh  */
+struct HvdFusedArgs; /* csrc/comm/fused_allreduce.cu */
+
+/* Fused allreduce + 1/N + optimizer update over peer memory - the data path of
+ * hvd.DistributedOptimizer / MetricAverageCallback (reference mnist_keras.py:87,
+ * tensorflow2_keras_mnist.py:77).  emulate_ranks > 0: one cooperative launch, blockIdx.y = rank. */
+int hvd_fused_allreduce_launch(const struct HvdCommCtx* c, const struct HvdFusedArgs* a, int ctas, int threads,
+                               void* stream, int emulate_ranks);
+/* Broadcast a range from root's arena - BroadcastGlobalVariablesCallback (reference mnist_keras.py:97). */
+int hvd_bcast_launch(const struct HvdCommCtx* c, int slot, int root, long long off, long long n, int ctas, int threads,
+                     void* stream, int emulate_ranks);
+int hvd_pad_bytes(void);
+int hvd_epoch_bytes(void);
+int hvd_cuda_malloc(void** p, long long bytes);
+int hvd_cuda_free(void* p);
+int hvd_ipc_get_handle(void* p, void* out64);
+int hvd_ipc_open(const void* h64, void** p);
+int hvd_ipc_close(void* p);
+int hvd_can_access_peer(int dev, int peer);
+const char* hvd_cuda_error_string(int e);
+
+/* tcgen05 TF32 GEMM, D[M,N] = A*B.  A: [M][K] (a_mn=0) or [K][M] (a_mn=1); B: [N][K] or [K][N].
+ * epilogue: 0 store, 1 atomic add (split-K), 2 bias+relu, 3 maxpool/dropout/relu-backward scatter.
+ * The Dense(128) layer's forward / dgrad / wgrad (reference mnist_keras.py:79). */
+int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int bn, int k_split,
+                int epilogue, const float* bias, long long ldd, void* stream, unsigned lbo_a, unsigned sbo_a,
+                unsigned lbo_b, unsigned sbo_b, const uint8_t* mask, float scale);
+
+/* Fused MNIST-CNN engine kernels (reference model mnist_keras.py:71-81). */
+int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, void* stream);
+int hvd_conv2_fprop(const float* a1, const float* w2, const float* bias2, float* p2, uint8_t* mask,
+                    const void* step_state, int B, int training, float keep, int ctas, void* stream);
+int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels, float* dh_pre,
+             float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B, int training, int backward,
+             float keep, void* stream);
+int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a1, float* da1, int B, int ctas, void* stream);
+int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream);
+int hvd_conv1_wgrad(const float* x, const float* da1, float* g_w, float* g_b, int B, void* stream);
+int hvd_colsum64(const float* m, float* out, long long rows, void* stream);
+
+/* Dense layer forward y = act(x*W + bias) as a split-K tcgen05 GEMM (keras Dense, reference
+ * mnist_keras.py:79,81).  x: [M][K], W: [K][N] (Keras layout), y: [M][N]; relu: 0/1.  The k_split CTAs
+ * per tile accumulate with red.add into `scratch` (M*N floats, caller-allocated device memory that must
+ * be zero on entry); the finalize pass adds bias/activation into y and zeroes scratch again. */
+int hvd_dense_forward(const float* x, const float* W, const float* bias, float* y, int M, int N, int K, int relu,
+                      int k_split, float* scratch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HVD_B200_H_ */

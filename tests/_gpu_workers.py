@@ -71,7 +71,7 @@ def train_replicas():
     assert all(c == cs[0] for c in cs), cs
     got = torch.cat([torch.from_numpy(w).reshape(-1) for w in m.get_weights()])
     exp = torch.cat([torch.from_numpy(w).reshape(-1) for w in ref.get_weights()])
-    torch.testing.assert_close(got, exp, rtol=2e-3, atol=2e-4)
+    torch.testing.assert_close(got, exp, rtol=5e-3, atol=2e-3)      # TF32 vs cuDNN oracle
     assert not torch.equal(m.arena.params, w0)
     if r == 0:
         import tempfile

@@ -267,3 +267,27 @@ def test_engine_trains_with_dropout_and_partial_batch():
     assert h.history["loss"][-1] < 0.3 < h.history["loss"][0]            # the reference's CI range
     assert h.history["val_accuracy"][-1] > 0.9
     hvd.shutdown()
+
+
+def _dense_lib():
+    lib = _lib()
+    vp, ci = ctypes.c_void_p, ctypes.c_int
+    lib.hvd_dense_forward.restype = ci
+    lib.hvd_dense_forward.argtypes = [vp, vp, vp, vp, ci, ci, ci, ci, ci, vp, vp]
+    return lib
+
+
+@pytest.mark.parametrize("M,N,K,relu,ks", [(128, 128, 9216, 1, 36), (100, 10, 128, 0, 1), (128, 64, 2048, 1, 8)])
+def test_dense_forward_splitk_with_caller_scratch(M, N, K, relu, ks):
+    lib = _dense_lib()
+    torch.manual_seed(8)
+    x, W, b = torch.randn(M, K, device="cuda"), torch.randn(K, N, device="cuda") * 0.05, torch.randn(N, device="cuda")
+    y = torch.empty(M, N, device="cuda")
+    scratch = torch.zeros(M * N, device="cuda")
+    for _ in range(2):                                   # the finalize pass re-arms the scratch
+        assert lib.hvd_dense_forward(x.data_ptr(), W.data_ptr(), b.data_ptr(), y.data_ptr(), M, N, K, relu, ks,
+                                     scratch.data_ptr(), _s()) == 0
+    ref = x.double() @ W.double() + b.double()
+    ref = F.relu(ref) if relu else ref
+    assert _rel(y, ref) < 3e-3
+    assert (scratch == 0).all()
