@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(float* __restrict__
 int hvd_dense_forward_impl(const float* x, const float* W, const float* bias, float* y, int M, int N, int K, int relu,
                            int k_split, float* scratch, cudaStream_t st) {
   if (M < 1 || N < 1 || K < 1 || k_split < 1 || !scratch) return -1;
+  if ((N & 3) || (K & 3)) return -2;     // TMA needs 16-byte row strides: K and N multiples of 4
   const int bn = (N % 128 == 0 || N > 64) ? 128 : 64;
   int rc = hvd_tc_gemm(x, W, scratch, M, N, K, /*a_mn=*/0, /*b_mn=*/1, bn, k_split, /*atomic add*/ 1, nullptr, N, st,
                        0, 0, 0, 0, nullptr, 1.0f);

@@ -118,7 +118,8 @@ int hvd_conv1_wgrad(const float* x, const float* da1, float* g_w, float* g_b, in
 int hvd_colsum64(const float* m, float* out, long long rows, void* stream);
 
 /* Dense layer forward y = act(x*W + bias) as a split-K tcgen05 GEMM (keras Dense, reference
- * mnist_keras.py:79,81).  x: [M][K], W: [K][N] (Keras layout), y: [M][N]; relu: 0/1.  The k_split CTAs
+ * mnist_keras.py:79,81).  x: [M][K], W: [K][N] (Keras layout), y: [M][N]; relu: 0/1; K and N must be
+ * multiples of 4 (TMA row strides are 16-byte granular; returns -2 otherwise).  The k_split CTAs
  * per tile accumulate with red.add into `scratch` (M*N floats, caller-allocated device memory that must
  * be zero on entry); the finalize pass adds bias/activation into y and zeroes scratch again. */
 int hvd_dense_forward(const float* x, const float* W, const float* bias, float* y, int M, int N, int K, int relu,

@@ -277,7 +277,7 @@ def _dense_lib():
     return lib
 
 
-@pytest.mark.parametrize("M,N,K,relu,ks", [(128, 128, 9216, 1, 36), (100, 10, 128, 0, 1), (128, 64, 2048, 1, 8)])
+@pytest.mark.parametrize("M,N,K,relu,ks", [(128, 128, 9216, 1, 36), (100, 16, 128, 0, 1), (128, 64, 2048, 1, 8)])
 def test_dense_forward_splitk_with_caller_scratch(M, N, K, relu, ks):
     lib = _dense_lib()
     torch.manual_seed(8)
