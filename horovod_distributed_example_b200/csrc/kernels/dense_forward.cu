@@ -42,3 +42,98 @@ extern "C" int hvd_dense_forward(const float* x, const float* W, const float* bi
                                  int relu, int k_split, float* scratch, void* stream) {
   return hvd_dense_forward_impl(x, W, bias, y, M, N, K, relu, k_split, scratch, (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------------
+// hvd_dense_forward_noalloc: the same Dense forward for callers that are not able to allocate
+// device memory.
+//
+// Who needs it: code that runs where cudaMalloc is off limits - a plugin living inside another
+// runtime's memory pool that forbids side allocations, a real-time / serving loop that must not
+// take the allocator's device-wide lock (cudaMalloc synchronises the device), or a host that was
+// handed a fixed memory budget at start-up.  Such a caller can still own x, W, bias and y, but it
+// has nowhere to get the M*N split-K accumulator that hvd_dense_forward asks for.
+//
+// Here the accumulator is a fixed array inside this library's device image.  It costs
+// HVD_DENSE_NOALLOC_MAX_ELEMS * 4 bytes (1 MiB) on EVERY GPU that loads libhvd_cuda.so, from load
+// until the process exits, whether or not this function is ever called.
+//
+// Rules for callers:
+//   * M*N must not exceed HVD_DENSE_NOALLOC_MAX_ELEMS; larger problems are refused with
+//     HVD_ERR_NOALLOC_TOO_LARGE and a message from hvd_dense_forward_noalloc_error().
+//   * The first call on each device looks up the array's device address (one-time set-up, with that
+//     device current).  Make that first call before you begin any stream capture on the device.
+//   * All calls on a device share the one array and it keeps whatever the previous call left in it;
+//     this function therefore clears the part it is about to use, on `stream`, before the GEMM.
+//     Two calls whose GPU work can overlap (different streams, or different host threads without
+//     ordering between their streams) race on the array and produce wrong results: serialise them.
+//   * Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+#include <string>
+
+#define HVD_DENSE_NOALLOC_MAX_ELEMS (256 * 1024)
+#define HVD_ERR_NOALLOC_TOO_LARGE (-100)
+#define HVD_ERR_NOALLOC_SETUP (-101)
+
+static __device__ __align__(256) float g_dense_noalloc_scratch[HVD_DENSE_NOALLOC_MAX_ELEMS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};     // device address of the array, per device ordinal
+thread_local std::string g_noalloc_err;
+
+// In host code `g_dense_noalloc_scratch` is only a stand-in symbol, not a device address: the real
+// address has to be asked for, per device, with that device current.
+int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    g_noalloc_err = std::string("cannot identify the current device: ") + cudaGetErrorString(e);
+    return HVD_ERR_NOALLOC_SETUP;
+  }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_dense_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      g_noalloc_err = std::string("cudaGetSymbolAddress(scratch) failed on device ") + std::to_string(dev) + ": " +
+                      cudaGetErrorString(e);
+      return HVD_ERR_NOALLOC_SETUP;
+    }
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" const char* hvd_dense_forward_noalloc_error() { return g_noalloc_err.c_str(); }
+extern "C" long long hvd_dense_forward_noalloc_max_elems() { return HVD_DENSE_NOALLOC_MAX_ELEMS; }
+
+extern "C" int hvd_dense_forward_noalloc(const float* x, const float* W, const float* bias, float* y, int M, int N,
+                                         int K, int relu, int k_split, void* stream) {
+  g_noalloc_err.clear();
+  if (M < 1 || N < 1 || K < 1 || k_split < 1) {
+    g_noalloc_err = "M, N, K and k_split must be positive";
+    return -1;
+  }
+  const long long need = (long long)M * N;
+  if (need > HVD_DENSE_NOALLOC_MAX_ELEMS) {
+    g_noalloc_err = "hvd_dense_forward_noalloc: M*N = " + std::to_string(need) + " output elements exceed the built-in "
+                    "scratch of " + std::to_string((long long)HVD_DENSE_NOALLOC_MAX_ELEMS) +
+                    " floats; use hvd_dense_forward with your own scratch buffer";
+    return HVD_ERR_NOALLOC_TOO_LARGE;
+  }
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // shared array, previous contents unknown: the accumulator region must start at zero
+  cudaError_t e = cudaMemsetAsync(scratch, 0, (size_t)need * sizeof(float), st);
+  if (e != cudaSuccess) {
+    g_noalloc_err = std::string("clearing the scratch failed: ") + cudaGetErrorString(e);
+    return (int)e;
+  }
+  return hvd_dense_forward_impl(x, W, bias, y, M, N, K, relu, k_split, scratch, st);
+}

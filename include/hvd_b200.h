@@ -125,6 +125,20 @@ int hvd_colsum64(const float* m, float* out, long long rows, void* stream);
 int hvd_dense_forward(const float* x, const float* W, const float* bias, float* y, int M, int N, int K, int relu,
                       int k_split, float* scratch, void* stream);
 
+/* Dense forward for callers that may not allocate device memory (plugins inside a foreign memory
+ * pool, latency-critical serving loops that must never hit cudaMalloc's device-wide lock, hosts with a
+ * fixed memory budget).  No counterpart in the reference: it exists only because hvd_dense_forward
+ * needs an M*N scratch accumulator that such callers cannot provide.  Same maths and arguments as
+ * hvd_dense_forward minus `scratch`: the accumulator is a 1 MiB array built into libhvd_cuda.so (held
+ * by every GPU that loads the library until exit).  Limit: M*N <= hvd_dense_forward_noalloc_max_elems()
+ * (262144); larger sizes return -100 with a message in hvd_dense_forward_noalloc_error().  The first
+ * call on a device does a one-time address look-up - make it before any stream capture.  All calls on
+ * a device share the array: calls whose GPU work may overlap race. */
+int hvd_dense_forward_noalloc(const float* x, const float* W, const float* bias, float* y, int M, int N, int K,
+                              int relu, int k_split, void* stream);
+long long hvd_dense_forward_noalloc_max_elems(void);
+const char* hvd_dense_forward_noalloc_error(void);
+
 #ifdef __cplusplus
 }
 #endif
