@@ -11,7 +11,7 @@
 #include <stdint.h>
 
 #define HVD_MAX_RANKS 8
-#define HVD_MAX_CTAS 160
+#define HVD_MAX_CTAS 320
 #define HVD_NUM_SLOTS 32
 
 struct HvdCommCtx {
@@ -52,6 +52,7 @@ __device__ __forceinline__ float4 ld_sys_f4(const float* p) {
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ float4 ld_f4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
   asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
                ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
@@ -75,6 +76,7 @@ __device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
 __device__ __forceinline__ void hvd_barrier(const HvdCommCtx& c, int slot, uint32_t epoch, bool release) {
   const int rank = hvd_rank(c);
   const int cta = blockIdx.x;
+  if (c.nranks == 1) { __syncthreads(); return; }        // single GPU: nothing to wait for
   if (release) __threadfence_system();
   __syncthreads();
   if ((int)threadIdx.x < c.nranks) {

@@ -114,7 +114,9 @@ __global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedAr
         const long long idx = i + (long long)u * blockDim.x;
 #pragma unroll
         for (int r = 0; r < HVD_MAX_RANKS; r++)
-          if (r < N && idx < i1) v[u][r] = ld_sys_f4(c.base[r] + a.grad_off + s + idx * 4);
+          if (r < N && idx < i1)          // own gradients: plain load (written by earlier kernels on this GPU)
+            v[u][r] = (r == rank) ? ld_f4(c.base[r] + a.grad_off + s + idx * 4)
+                                  : ld_sys_f4(c.base[r] + a.grad_off + s + idx * 4);
       }
 #pragma unroll
       for (int u = 0; u < kUnroll; u++) {
@@ -143,7 +145,10 @@ __global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedAr
       } else if (VARIANT == HVD_TWOSHOT) {
 #pragma unroll
         for (int r = 0; r < HVD_MAX_RANKS; r++)
-          if (r < N) st_sys_f4(c.base[r] + dst_off, res);
+          if (r < N) {
+            if (r == rank) *reinterpret_cast<float4*>(mine + dst_off) = res;
+            else st_sys_f4(c.base[r] + dst_off, res);
+          }
       } else {
         multimem_st_f4(c.mc_base + dst_off, res);
       }

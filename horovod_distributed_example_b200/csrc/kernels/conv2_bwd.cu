@@ -239,7 +239,7 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         if (tap < 9) {
           float* d = p.g_w + ((long long)tap * 32 + (r & 31)) * 64 + c;
 #pragma unroll
-          for (int j = 0; j < 32; j++) atomicAdd(d + j, v[j]);
+          for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
         } else if (tap == 9 && (r & 31) == 0) {   // the ones "tap": every row holds sum_pixels dY2[co]
 #pragma unroll
           for (int j = 0; j < 32; j++) atomicAdd(p.g_b + c + j, v[j]);
@@ -298,7 +298,7 @@ extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, fl
   }
   wg::Params p;
   p.B = B; p.n_patches = B * 9;
-  if (ctas <= 0) ctas = 144;
+  if (ctas <= 0) ctas = 72;
   p.patches_per_cta = (p.n_patches + ctas - 1) / ctas;
   ctas = (p.n_patches + p.patches_per_cta - 1) / p.patches_per_cta;
   p.g_w = g_w; p.g_b = g_b;

@@ -148,10 +148,12 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(HeadParams p) {
     float acc = 0.f;
     if (o < HID * NCLS) {
       const int j = o / NCLS, k = o % NCLS;
+#pragma unroll 8
       for (int b = 0; b < p.B; b++) acc = fmaf(h[b * HID + j], dl[b * NCLS + k], acc);
       p.g_w2[o] = acc;
     } else {
       const int k = o - HID * NCLS;
+#pragma unroll 8
       for (int b = 0; b < p.B; b++) acc += dl[b * NCLS + k];
       p.g_b2[k] = acc;
     }
@@ -170,6 +172,7 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(HeadParams p) {
   __syncthreads();
   for (int j = tid; j < HID; j += nt) {
     float acc = 0.f;
+#pragma unroll 8
     for (int b = 0; b < p.B; b++) acc += h[b * HID + j];
     p.g_b1[j] = acc;
   }

@@ -161,8 +161,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       } else if (row < p.M) {
         float* d = p.D + (long long)row * p.ldd + n0 + c;
         if (p.epilogue == EPI_ATOMIC_ADD) {
+          if (n0 + c + 32 <= p.N && (p.ldd & 3) == 0) {
 #pragma unroll
-          for (int j = 0; j < 32; j++) if (n0 + c + j < p.N) atomicAdd(d + j, v[j]);
+            for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            for (int j = 0; j < 32; j++) if (n0 + c + j < p.N) atomicAdd(d + j, v[j]);
+          }
         } else {
           if (p.epilogue == EPI_BIAS_RELU) {
 #pragma unroll

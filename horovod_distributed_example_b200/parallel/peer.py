@@ -33,7 +33,7 @@ from .. import basics
 from ..ops import native
 
 MAX_RANKS = 8
-MAX_CTAS = 160
+MAX_CTAS = 320
 NUM_SLOTS = 32
 
 # slots of the signal pad

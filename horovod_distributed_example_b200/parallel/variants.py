@@ -49,7 +49,7 @@ def reload():
 def default_ctas(nbytes: int, variant: int, nranks: int) -> int:
     """Enough CTAs to keep ~2 MB in flight on NVLink for large messages, one for tiny ones."""
     work = nbytes if variant == ONESHOT else max(nbytes // max(nranks, 1), 1)
-    return int(max(1, min(64, (work + 32767) // 32768)))
+    return int(max(1, min(148, (work + 16383) // 16384)))      # <= one CTA per SM: always co-resident
 
 
 def pick(nbytes: int, nranks: int, has_nvls: bool, forced: str = "auto", forced_ctas: int = 0

@@ -262,7 +262,7 @@ def test_engine_trains_with_dropout_and_partial_batch():
     x = (x[..., None] / 255.0).astype(np.float32)
     xt = (xt[..., None] / 255.0).astype(np.float32)
     m = build()
-    h = m.fit(x, y, batch_size=128, epochs=3, verbose=0, validation_data=(xt, yt))
+    h = m.fit(x, y, batch_size=128, epochs=6, verbose=0, validation_data=(xt, yt))
     assert type(m._backend).__name__ == "MnistEngine"
     assert h.history["loss"][-1] < 0.3 < h.history["loss"][0]            # the reference's CI range
     assert h.history["val_accuracy"][-1] > 0.9
