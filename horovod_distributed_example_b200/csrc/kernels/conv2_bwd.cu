@@ -1,18 +1,22 @@
 // conv2 backward on tcgen05 / TMEM / TMA (reference layer: Conv2D(64,(3,3)) at mnist_keras.py:75).
 //
 // dgrad  da1[b,y,x,ci] = relu'(a1) * sum_{kh,kw,co} dY2[b,y-kh,x-kw,co] * W2[kh,kw,ci,co]
-//        implicit GEMM: M = 26x26 output pixels in 13x9 boxes (117 of 128 rows used), N = 32 ci,
-//        K = 9 taps x 64 co in 18 blocks of 32.  A = 4-D TMA boxes of dY2 at NEGATIVE offsets - the
-//        "full" convolution's zero padding is TMA out-of-bounds fill, no padded copy exists.
+//        implicit GEMM: M = 16x8 output pixels per tile, N = 32 ci, K = 9 taps x 64 co.  A = ONE haloed
+//        4-D TMA box of dY2 per channel half ({32 co, 10 w, 18 h}) at NEGATIVE offsets - the "full"
+//        convolution's zero padding is TMA out-of-bounds fill, no padded copy exists - and the 9 taps
+//        are row-shifted descriptors into that tile (group stride 10 rows), 5.9x less L2 traffic than
+//        a box per tap.
 //        B = W2[tap] as [ci][co] (co contiguous = K-major), whole kernel resident in smem.
 //        Epilogue applies conv1's ReLU mask and stores da1.
 //
 // wgrad  dW2[kh,kw,ci,co] = sum_{b,oy,ox} a1[b,oy+kh,ox+kw,ci] * dY2[b,oy,ox,co]
 //        the reduction runs over pixels, so BOTH operands are MN-major: A[(tap,ci)][pixel] and
-//        B[co][pixel] are the activation tensors themselves ([pixel][channel] rows).  M = 4 taps x
-//        32 ci per accumulator, three accumulators in TMEM (taps 0-3, 4-7, 8 + a tile of ones whose
-//        "tap" yields the bias gradient for free).  Each CTA reduces a slice of the pixels
-//        (split-K over 8x8 patches) and adds its 288x64 result into the arena with red.add.
+//        B[co][pixel] are the activation tensors themselves ([pixel][channel] rows).  One haloed a1
+//        tile (10x10 pixels) per patch serves all 9 taps: per kernel row kh the M atoms are the kw
+//        shifts of the same rows (LBO = one row = 128 B, i.e. overlapping atoms).  Four accumulators
+//        in TMEM: kh = 0,1,2 and one fed by 1 KB of ones that yields the bias gradient for free.
+//        Each CTA reduces a slice of the pixels (split-K over 8x8 patches) and adds its 288x64 result
+//        into the arena with red.add.v4.
 #include "mnist_common.cuh"
 #include "tc_common.cuh"
 
@@ -21,13 +25,15 @@ using namespace mnist;
 
 // ============================================================================ dgrad
 namespace dg {
-constexpr int STAGES = 6;
-constexpr int A_STAGE = 128 * 128;
-constexpr int A_TX = 117 * 128;             // bytes one 13x9 box delivers
+constexpr int STAGES = 4;
+constexpr int A_STAGE = 24 * 1024;          // box {32 co, 10 w, 18 h, 1 n} = 180 rows x 128 B (23,040 B)
+constexpr int A_TX = 180 * 128;
 constexpr int W_BYTES = 18 * 4096;
 constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 1024 + 256;
 constexpr int TMEM_COLS = 64;               // 2 stages x 32 columns
-constexpr int BW = 13, BH = 9;              // box: 13 wide, 9 high -> 2 x 3 boxes per 26x26 image
+constexpr int TH = 16, TW = 8;              // output tile: 16 rows x 8 columns = 128 pixels
+constexpr int TILES_X = 4;                  // 26 = 3*8 + 2 -> 4 column tiles; 26 = 16 + 10 -> 2 row tiles
+constexpr uint32_t SBO_HALO = 10 * 128;
 
 struct Params {
   int B, n_tiles;
@@ -58,13 +64,6 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
-  // rows 117..127 of every A stage are never written by TMA: zero them once so no NaN bit
-  // patterns ever enter the tensor core (their accumulator rows are discarded anyway)
-  for (int i = threadIdx.x; i < STAGES * 11 * 32; i += blockDim.x) {
-    const int s = i / (11 * 32), r = i % (11 * 32);
-    reinterpret_cast<float*>(sA + s * A_STAGE + 117 * 128)[r] = 0.f;
-  }
-  tc::fence_proxy_async();
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -77,13 +76,14 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         for (int h = 0; h < 2; h++) tc::tma_load_2d(sW + (t * 2 + h) * 4096, &tmW, wfull, 32 * h, t * 32);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-        const int b = tile / 6, ty = (tile % 6) / 2, tx = tile % 2;
-        for (int kb = 0; kb < 18; kb++, it++) {
+        const int b = tile / 8, ty = (tile % 8) / TILES_X, tx = tile % TILES_X;
+        for (int half = 0; half < 2; half++, it++) {
           const int s = it % STAGES;
           tc::mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
           tc::mbar_expect_tx(&full[s], A_TX);
-          const int tap = kb >> 1, kh = tap / 3, kw = tap % 3;
-          tc::tma_load_4d(sA + s * A_STAGE, &tmG, &full[s], 32 * (kb & 1), tx * BW - kw, ty * BH - kh, b);
+          // haloed dY2 tile: origin (x0-2, y0-2); everything outside 24x24 is TMA zero fill = the
+          // "full" convolution's padding
+          tc::tma_load_4d(sA + s * A_STAGE, &tmG, &full[s], 32 * half, tx * TW - 2, ty * TH - 2, b);
         }
       }
     }
@@ -96,15 +96,22 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         const int as = ti & 1;
         tc::mbar_wait(&acce[as], ((ti >> 1) & 1) ^ 1);
         tc::tc_fence_after();
-        for (int kb = 0; kb < 18; kb++, it++) {
+        for (int half = 0; half < 2; half++, it++) {
           const int s = it % STAGES;
           tc::mbar_wait(&full[s], (it / STAGES) & 1);
           tc::tc_fence_after();
           const uint32_t a = tc::smem_u32(sA + s * A_STAGE);
-          const uint32_t w = tc::smem_u32(sW + kb * 4096);
 #pragma unroll
-          for (int k = 0; k < 4; k++)
-            tc::mma_tf32(tmem + as * 32, tc::desc_kmajor(a + k * 32), tc::desc_kmajor(w + k * 32), idesc, (kb | k) != 0);
+          for (int tap = 0; tap < 9; tap++) {
+            const int kh = tap / 3, kw = tap % 3;
+            // output (y,x) needs dY2[y-kh][x-kw] = halo row (y+2-kh)*10 + (x+2-kw)
+            const uint32_t a_tap = a + ((2 - kh) * 10 + (2 - kw)) * 128;
+            const uint32_t w = tc::smem_u32(sW + (tap * 2 + half) * 4096);
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+              tc::mma_tf32(tmem + as * 32, tc::make_smem_desc(a_tap + k * 32, 16, SBO_HALO, 2),
+                           tc::desc_kmajor(w + k * 32), idesc, (half | tap | k) != 0);
+          }
           tc::mma_commit(&empty[s]);
         }
         tc::mma_commit(&accf[as]);
@@ -112,7 +119,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     }
   } else if (warp >= 4) {
     const int q = warp & 3;
-    const int r = q * 32 + lane;
+    const int r = q * 32 + lane;               // accumulator row: y = r/8, x = r%8 inside the tile
     int ti = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
       const int as = ti & 1;
@@ -123,9 +130,9 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       tc::tmem_ld_wait();
       tc::tc_fence_before();
       tc::mbar_arrive(&acce[as]);
-      const int b = tile / 6, ty = (tile % 6) / 2, tx = tile % 2;
-      const int y = ty * BH + r / BW, x = tx * BW + r % BW;
-      if (r < BW * BH && y < H1) {
+      const int b = tile / 8, ty = (tile % 8) / TILES_X, tx = tile % TILES_X;
+      const int y = ty * TH + (r >> 3), x = tx * TW + (r & 7);
+      if (y < H1 && x < H1) {
         const long long off = (((long long)b * H1 + y) * H1 + x) * C1;
         const float4* act = reinterpret_cast<const float4*>(p.a1 + off);
         float4* dst = reinterpret_cast<float4*>(p.da1 + off);
@@ -146,12 +153,15 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
 
 // ============================================================================ wgrad
 namespace wg {
-constexpr int SLOT = 8192;                  // one 8x8-pixel box of 32 channels
-constexpr int STAGE = 12 * SLOT;            // 9 taps | ones | dY2 lo | dY2 hi
-constexpr int STAGE_TX = 11 * SLOT;         // the ones slot is not loaded
-constexpr int STAGES = 2;
-constexpr int SMEM_BYTES = STAGES * STAGE + 1024 + 256;
-constexpr int TMEM_COLS = 256;              // 3 accumulators x 64 columns
+constexpr int HALO_BYTES = 13 * 1024;       // box {32 ci, 10 w, 10 h, 1 n} = 100 rows x 128 B (12,800 B)
+constexpr int HALO_TX = 100 * 128;
+constexpr int DY_SLOT = 8192;               // box {32 co, 8 w, 8 h, 1 n}
+constexpr int STAGE = HALO_BYTES + 2 * DY_SLOT + 1024;   // + slack so the dummy 4th atom stays in bounds
+constexpr int STAGE_TX = HALO_TX + 2 * DY_SLOT;
+constexpr int STAGES = 4;
+constexpr int ONES_BYTES = 1024;            // 8 k-rows of ones, shared by all four M atoms (LBO = 0)
+constexpr int SMEM_BYTES = STAGES * STAGE + ONES_BYTES + 1024 + 256;
+constexpr int TMEM_COLS = 256;              // kh = 0,1,2 accumulators + the bias accumulator, 64 columns each
 
 struct Params {
   int B, n_patches, patches_per_cta;
@@ -163,7 +173,8 @@ __global__ void __launch_bounds__(256, 1)
 conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmG, Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE);
+  uint8_t* sOnes = smem + STAGES * STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sOnes + ONES_BYTES);
   uint64_t* full = bars;
   uint64_t* empty = bars + STAGES;
   uint64_t* accf = bars + 2 * STAGES;
@@ -180,10 +191,10 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
-  for (int i = threadIdx.x; i < STAGES * (SLOT / 4); i += blockDim.x) {       // the tile of ones (bias gradient)
-    const int s = i / (SLOT / 4), r = i % (SLOT / 4);
-    reinterpret_cast<float*>(smem + s * STAGE + 9 * SLOT)[r] = 1.0f;
-  }
+  for (int i = threadIdx.x; i < ONES_BYTES / 4; i += blockDim.x) reinterpret_cast<float*>(sOnes)[i] = 1.0f;
+  // the slack rows after each halo tile are read by the dummy 4th atom: keep them finite
+  for (int i = threadIdx.x; i < STAGES * 128; i += blockDim.x)       // rows 100..103 of each halo slot
+    reinterpret_cast<float*>(smem + (i / 128) * STAGE + HALO_TX)[i % 128] = 0.f;
   tc::fence_proxy_async();
   tc::tc_fence_before();
   __syncthreads();
@@ -199,50 +210,51 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int patch = p_begin + i;
         const int b = patch / 9, py = (patch % 9) / 3, px = patch % 3;
         uint8_t* st = smem + s * STAGE;
-        for (int t = 0; t < 9; t++) tc::tma_load_4d(st + t * SLOT, &tmA, &full[s], 0, px * 8 + t % 3, py * 8 + t / 3, b);
-        tc::tma_load_4d(st + 10 * SLOT, &tmG, &full[s], 0, px * 8, py * 8, b);
-        tc::tma_load_4d(st + 11 * SLOT, &tmG, &full[s], 32, px * 8, py * 8, b);
+        tc::tma_load_4d(st, &tmA, &full[s], 0, px * 8, py * 8, b);                       // a1 halo, once
+        tc::tma_load_4d(st + HALO_BYTES, &tmG, &full[s], 0, px * 8, py * 8, b);           // dY2 co 0..31
+        tc::tma_load_4d(st + HALO_BYTES + DY_SLOT, &tmG, &full[s], 32, px * 8, py * 8, b);  // dY2 co 32..63
       }
     }
   } else if (warp == 1) {
     if (tc::elect_one()) {
       constexpr uint32_t idesc = tc::make_idesc_tf32(128, 64, 1, 1);
+      const uint32_t ones = tc::smem_u32(sOnes);
       for (int i = 0; i < np; i++) {
         const int s = i % STAGES;
         tc::mbar_wait(&full[s], (i / STAGES) & 1);
         tc::tc_fence_after();
-        const uint32_t st = tc::smem_u32(smem + s * STAGE);
+        const uint32_t halo = tc::smem_u32(smem + s * STAGE);
+        const uint32_t dy = halo + HALO_BYTES;
 #pragma unroll
-        for (int g = 0; g < 3; g++)
+        for (int ks = 0; ks < 8; ks++) {       // output row ks of the patch = 8 pixels = one K=8 MMA step
+          const uint64_t db = tc::desc_mnmajor(dy + ks * 1024, DY_SLOT);
 #pragma unroll
-          for (int ks = 0; ks < 8; ks++)     // 64 pixels = 8 MMAs of K=8
-            tc::mma_tf32(tmem + g * 64, tc::desc_mnmajor(st + g * 4 * SLOT + ks * 1024, SLOT),
-                         tc::desc_mnmajor(st + 10 * SLOT + ks * 1024, SLOT), idesc, (i | ks) != 0);
+          for (int kh = 0; kh < 3; kh++)       // M atoms = kw 0,1,2 (+1 dummy): the SAME halo rows shifted by one row each
+            tc::mma_tf32(tmem + kh * 64, tc::make_smem_desc(halo + (ks + kh) * 10 * 128, 128, 512, 1), db, idesc,
+                         (i | ks) != 0);
+          tc::mma_tf32(tmem + 192, tc::make_smem_desc(ones, 0, 512, 1), db, idesc, (i | ks) != 0);   // bias gradient
+        }
         tc::mma_commit(&empty[s]);
       }
       tc::mma_commit(accf);
     }
   } else if (warp >= 4 && np > 0) {
     const int q = warp & 3;
-    const int r = q * 32 + lane;              // accumulator row: tap-in-group = r/32, ci = r%32
-    tc::mbar_wait(accf, 0);
+    tc::mbar_wait(accf, 0);                   // accumulator row: kw = q, ci = lane
     tc::tc_fence_after();
 #pragma unroll 1
-    for (int g = 0; g < 3; g++) {
-      const int tap = g * 4 + (r >> 5);
-      if (g == 2 && q >= 2) break;            // rows 64..127 of the last accumulator are padding
+    for (int g = 0; g < 4; g++) {
+      if (g < 3 && q == 3) continue;          // 4th atom of a kh accumulator is the dummy shift
+      if (g == 3 && q != 0) continue;         // bias accumulator: every row is the same column sum (warp-uniform skip)
 #pragma unroll 1
       for (int c = 0; c < 64; c += 32) {
         float v[32];
         tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + g * 64 + c, v);
         tc::tmem_ld_wait();
-        if (tap < 9) {
-          float* d = p.g_w + ((long long)tap * 32 + (r & 31)) * 64 + c;
+        float* d = (g < 3) ? p.g_w + ((long long)(g * 3 + q) * 32 + lane) * 64 + c : p.g_b + c;
+        if (g < 3 || lane == 0) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
-        } else if (tap == 9 && (r & 31) == 0) {   // the ones "tap": every row holds sum_pixels dY2[co]
-#pragma unroll
-          for (int j = 0; j < 32; j++) atomicAdd(p.g_b + c + j, v[j]);
         }
       }
     }
@@ -260,7 +272,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
   {
     uint64_t dims[4] = {64, 24, 24, (uint64_t)B};
     uint64_t str[3] = {256, 24 * 256, 24 * 24 * 256};
-    uint32_t box[4] = {32, dg::BW, dg::BH, 1};
+    uint32_t box[4] = {32, 10, 18, 1};
     if (tc::make_tmap(&tmG, dy2, 4, dims, str, box)) return -2;
     uint64_t wd[2] = {64, 288};
     uint64_t ws[1] = {256};
@@ -272,7 +284,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
     if (cudaFuncSetAttribute(dg::conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dg::SMEM_BYTES) != cudaSuccess) return -10;
     attr = true;
   }
-  dg::Params p{B, B * 6, a1, da1};
+  dg::Params p{B, B * 8, a1, da1};
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
   dg::conv2_dgrad_kernel<<<ctas, 256, dg::SMEM_BYTES, (cudaStream_t)stream>>>(tmG, tmW, p);
@@ -285,10 +297,11 @@ extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, fl
   {
     uint64_t dims[4] = {32, 26, 26, (uint64_t)B};
     uint64_t str[3] = {128, 26 * 128, 26 * 26 * 128};
-    uint32_t box[4] = {32, 8, 8, 1};
-    if (tc::make_tmap(&tmA, a1, 4, dims, str, box, true)) return -2;
+    uint32_t hbox[4] = {32, 10, 10, 1};
+    if (tc::make_tmap(&tmA, a1, 4, dims, str, hbox, true)) return -2;
     uint64_t gd[4] = {64, 24, 24, (uint64_t)B};
     uint64_t gs[3] = {256, 24 * 256, 24 * 24 * 256};
+    uint32_t box[4] = {32, 8, 8, 1};
     if (tc::make_tmap(&tmG, dy2, 4, gd, gs, box, true)) return -3;
   }
   static bool attr = false;
@@ -298,7 +311,7 @@ extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, fl
   }
   wg::Params p;
   p.B = B; p.n_patches = B * 9;
-  if (ctas <= 0) ctas = 72;
+  if (ctas <= 0) ctas = 144;
   p.patches_per_cta = (p.n_patches + ctas - 1) / ctas;
   ctas = (p.n_patches + p.patches_per_cta - 1) / p.patches_per_cta;
   p.g_w = g_w; p.g_b = g_b;

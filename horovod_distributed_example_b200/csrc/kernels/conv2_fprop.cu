@@ -2,10 +2,15 @@
 // (reference layers: mnist_keras.py:75-78).  Implicit GEMM on tcgen05 / TMEM fed by TMA:
 //
 //   M = output pixels (B*24*24 = 73,728), N = 64 output channels, K = 9 taps x 32 input channels.
-//   An M tile is two 8x8 spatial patches (128 pixels), so every 2x2 pool window lies inside one
-//   tile and inside one warp's 32 TMEM lanes: pooling is two __shfl_xor per value in the epilogue.
-//   A (im2col) is never materialised: for tap (kh,kw) the K-slice of a patch is the 4-D TMA box
-//   {32 ch, 8 w, 8 h, 1 n} of a1 at (0, ow0+kw, oh0+kh, n) - 64 rows of 128 B, 128B-swizzled.
+//   An M tile is the same 8x8 spatial patch of two consecutive images (128 pixels), so every 2x2
+//   pool window lies inside one tile and inside one warp's 32 TMEM lanes: pooling is two __shfl_xor
+//   per value in the epilogue.
+//   A (im2col) is never materialised, and the 9 taps do not re-read their inputs: per kernel row kh
+//   ONE 4-D TMA box {32 ch, 10 w, 8 h, 2 n} brings a 10-wide halo (160 rows of 128 B, 128B-swizzled)
+//   and the three kw taps are the same smem tile read through descriptors whose start is shifted by
+//   kw rows with a group stride of 10 rows (SBO = 1280 B).  The tensor core swizzles on absolute
+//   address bits, so shifted starts and non-power-of-two strides are legal (profiles/
+//   desc_probe_shifted_descriptors.json).  2.45x less L2->smem traffic than one box per tap.
 //   B = the whole HWIO kernel (72 KB) stays resident in smem for the life of the persistent CTA;
 //   per tap it is [32 cin][64 cout] with cout contiguous = an MN-major operand (2 atoms of 32).
 //
@@ -20,10 +25,13 @@ namespace {
 using namespace mnist;
 
 constexpr int STAGES = 4;
-constexpr int A_STAGE = 128 * 128;          // 2 patches x 64 rows x 128 B
+constexpr int A_STAGE = 20 * 1024;          // one kh: box {32 c, 10 w, 8 h, 2 n} = 160 rows x 128 B
 constexpr int W_BYTES = 9 * 8192;           // 9 taps x [32 cin][64 cout] fp32
 constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 1024 + 256;
 constexpr int TMEM_COLS = 128;              // 2 accumulator stages x 64 columns
+constexpr int EPI_WARPS = 8;                // 2 per TMEM lane quadrant (one per 32-column chunk)
+constexpr int THREADS = 128 + EPI_WARPS * 32;
+constexpr uint32_t SBO_HALO = 10 * 128;     // next output row = 10 halo rows further
 
 struct Params {
   int B, n_tiles, training;
@@ -34,7 +42,7 @@ struct Params {
   const StepState* st;
 };
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(THREADS, 1)
 conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -53,7 +61,7 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
     tc::mbar_init(wfull, 1);
-    for (int s = 0; s < 2; s++) { tc::mbar_init(&accf[s], 1); tc::mbar_init(&acce[s], 128); }
+    for (int s = 0; s < 2; s++) { tc::mbar_init(&accf[s], 1); tc::mbar_init(&acce[s], EPI_WARPS * 32); }
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -61,7 +69,6 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const int n_patches = p.B * 9;
 
   if (warp == 0) {
     if (tc::elect_one()) {
@@ -70,17 +77,13 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         for (int j = 0; j < 2; j++) tc::tma_load_2d(sW + t * 8192 + j * 4096, &tmW, wfull, 32 * j, t * 32);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-        for (int tap = 0; tap < 9; tap++, it++) {
+        const int ip = tile / 9, py = (tile % 9) / 3, px = tile % 3;
+        for (int kh = 0; kh < 3; kh++, it++) {
           const int s = it % STAGES;
           tc::mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
           tc::mbar_expect_tx(&full[s], A_STAGE);
-          const int kh = tap / 3, kw = tap % 3;
-#pragma unroll
-          for (int h = 0; h < 2; h++) {
-            const int patch = 2 * tile + h;        // patch >= n_patches reads n >= B: TMA zero-fills
-            const int b = patch / 9, py = (patch % 9) / 3, px = patch % 3;
-            tc::tma_load_4d(sA + s * A_STAGE + h * 8192, &tmA, &full[s], 0, px * 8 + kw, py * 8 + kh, b);
-          }
+          // rows kh..kh+7 of the 10-wide halo of BOTH images of the pair (image >= B: TMA zero-fills)
+          tc::tma_load_4d(sA + s * A_STAGE, &tmA, &full[s], 0, px * 8, py * 8 + kh, 2 * ip);
         }
       }
     }
@@ -93,82 +96,96 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int as = ti & 1;
         tc::mbar_wait(&acce[as], ((ti >> 1) & 1) ^ 1);
         tc::tc_fence_after();
-        for (int tap = 0; tap < 9; tap++, it++) {
+        for (int kh = 0; kh < 3; kh++, it++) {
           const int s = it % STAGES;
           tc::mbar_wait(&full[s], (it / STAGES) & 1);
           tc::tc_fence_after();
           const uint32_t a = tc::smem_u32(sA + s * A_STAGE);
-          const uint32_t w = tc::smem_u32(sW + tap * 8192);
 #pragma unroll
-          for (int k = 0; k < 4; k++)
-            tc::mma_tf32(tmem + as * 64, tc::desc_kmajor(a + k * 32), tc::desc_mnmajor(w + k * 1024, 4096), idesc,
-                         (tap | k) != 0);
+          for (int kw = 0; kw < 3; kw++) {
+            const uint32_t w = tc::smem_u32(sW + (kh * 3 + kw) * 8192);
+#pragma unroll
+            for (int k = 0; k < 4; k++)     // the tap shift is a row offset into the shared halo tile
+              tc::mma_tf32(tmem + as * 64, tc::make_smem_desc(a + kw * 128 + k * 32, 16, SBO_HALO, 2),
+                           tc::desc_mnmajor(w + k * 1024, 4096), idesc, (kh | kw | k) != 0);
+          }
           tc::mma_commit(&empty[s]);
         }
         tc::mma_commit(&accf[as]);
       }
     }
   } else if (warp >= 4) {
-    const int q = warp & 3;
+    const int q = warp & 3;                      // TMEM lane quadrant
+    const int c = (warp - 4) >> 2;               // which 32-channel chunk this warp handles
     const int r = q * 32 + lane;                 // accumulator row = pixel inside the tile
     const int half = r >> 6, hl = (r & 63) >> 3, wl = r & 7;
-    const bool owner = (lane & 9) == 0;          // even h, even w: writes the pooled element
+    const int wp = (lane & 1) | ((lane >> 2) & 2);   // position inside the 2x2 window (dy*2+dx)
+    const int base = lane & ~9;
     const unsigned step = p.st->step, seed = p.st->seed;
     const float inv_keep = 1.0f / p.keep;
+    float bias[32];
+#pragma unroll
+    for (int j = 0; j < 32; j++) bias[j] = __ldg(p.bias + c * 32 + j);
     int ti = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
       const int as = ti & 1;
       tc::mbar_wait(&accf[as], (ti >> 1) & 1);
       tc::tc_fence_after();
-      float v[2][32];
-      tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + as * 64, v[0]);
-      tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + as * 64 + 32, v[1]);
+      float v[32];
+      tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + as * 64 + c * 32, v);
       tc::tmem_ld_wait();
       tc::tc_fence_before();
       tc::mbar_arrive(&acce[as]);                // TMEM stage is free: next tile's MMAs may start
-      const int patch = 2 * tile + half;
-      const int b = patch / 9, py = (patch % 9) / 3, px = patch % 3;
+      const int ip = tile / 9, py = (tile % 9) / 3, px = tile % 3;
+      const int b = 2 * ip + half;
       const int ph = py * 4 + (hl >> 1), pw = px * 4 + (wl >> 1);
-      const long long obase = (((long long)b * HP + ph) * HP + pw) * C2;
+      const long long obase = (((long long)b * HP + ph) * HP + pw) * C2 + c * 32;
+      unsigned flags = 0;
 #pragma unroll
-      for (int c = 0; c < 2; c++) {
-        unsigned flags = 0;
-        float m[32];
+      for (int j = 0; j < 32; j++) {
+        const float x = fmaxf(v[j] + bias[j], 0.f);
+        float mx = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+        v[j] = mx;                               // every lane of the window now holds the window max
+        flags |= (x == mx ? 1u : 0u) << j;
+      }
+      // arg-max bookkeeping in the window's canonical order (pos 0,1,2; else 3)
+      const unsigned f0 = __shfl_sync(0xffffffffu, flags, base);
+      const unsigned f1 = __shfl_sync(0xffffffffu, flags, base | 1);
+      const unsigned f2 = __shfl_sync(0xffffffffu, flags, base | 8);
+      if (b < p.B) {
+        // the four lanes of a window split its 32 channels: lane `wp` finishes channels 8*wp..8*wp+7
+        uint32_t mb[2];
+        float o[8];
 #pragma unroll
-        for (int j = 0; j < 32; j++) {
-          const float x = fmaxf(v[c][j] + __ldg(p.bias + c * 32 + j), 0.f);
-          float mx = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 1));
-          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-          m[j] = mx;
-          flags |= (x == mx ? 1u : 0u) << j;
-        }
-        const unsigned f1 = __shfl_xor_sync(0xffffffffu, flags, 1);
-        const unsigned f8 = __shfl_xor_sync(0xffffffffu, flags, 8);
-        if (owner && patch < n_patches) {
-          uint32_t mb[8];
+        for (int h4 = 0; h4 < 2; h4++) {
+          uint4 rnd = make_uint4(0, 0, 0, 0);
+          if (p.training)
+            rnd = philox4x32_10(make_uint4((unsigned)((obase + 8 * wp) >> 2) + h4, step, 0x2u, 0u), make_uint2(seed, 0x5EEDu));
+          const unsigned rr[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
+          uint32_t packed = 0;
 #pragma unroll
-          for (int j4 = 0; j4 < 8; j4++) {
-            uint4 rnd = make_uint4(0, 0, 0, 0);
-            if (p.training) rnd = philox4x32_10(make_uint4((unsigned)((obase + c * 32) >> 2) + j4, step, 0x2u, 0u), make_uint2(seed, 0x5EEDu));
-            const unsigned rr[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
-            float o[4];
-            uint32_t packed = 0;
+          for (int e = 0; e < 4; e++) {
+            const int jj = h4 * 4 + e;           // 0..7 within this lane's slice
+            float m = 0.f;
+            unsigned b0 = 0, b1 = 0, b2 = 0;
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
-              const int j = j4 * 4 + e;
-              const unsigned pos = ((flags >> j) & 1) ? 0u : ((f1 >> j) & 1) ? 1u : ((f8 >> j) & 1) ? 2u : 3u;
-              const bool keep = !p.training || u01(rr[e]) < p.keep;
-              const float val = keep ? (p.training ? m[j] * inv_keep : m[j]) : 0.f;
-              o[e] = val;
-              packed |= (pos | ((keep && m[j] > 0.f) ? MASK_LIVE : 0u)) << (8 * e);
-            }
-            mb[j4] = packed;
-            *reinterpret_cast<float4*>(p.p2 + obase + c * 32 + j4 * 4) = make_float4(o[0], o[1], o[2], o[3]);
+            for (int w4 = 0; w4 < 4; w4++)       // select channel 8*wp+jj without dynamic register indexing
+              if (w4 == wp) {
+                m = v[w4 * 8 + jj];
+                b0 = (f0 >> (w4 * 8 + jj)) & 1; b1 = (f1 >> (w4 * 8 + jj)) & 1; b2 = (f2 >> (w4 * 8 + jj)) & 1;
+              }
+            const unsigned pos = b0 ? 0u : b1 ? 1u : b2 ? 2u : 3u;
+            const bool keep = !p.training || u01(rr[e]) < p.keep;
+            o[jj] = keep ? (p.training ? m * inv_keep : m) : 0.f;
+            packed |= (pos | ((keep && m > 0.f) ? MASK_LIVE : 0u)) << (8 * e);
           }
-          uint4* mp = reinterpret_cast<uint4*>(p.mask + obase + c * 32);
-          mp[0] = make_uint4(mb[0], mb[1], mb[2], mb[3]);
-          mp[1] = make_uint4(mb[4], mb[5], mb[6], mb[7]);
+          mb[h4] = packed;
         }
+        float4* dst = reinterpret_cast<float4*>(p.p2 + obase + 8 * wp);
+        dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+        dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+        *reinterpret_cast<uint2*>(p.mask + obase + 8 * wp) = make_uint2(mb[0], mb[1]);
       }
     }
   }
@@ -187,7 +204,7 @@ extern "C" int hvd_conv2_fprop(const float* a1, const float* w2, const float* bi
   {
     uint64_t dims[4] = {32, 26, 26, (uint64_t)B};
     uint64_t str[3] = {128, 26 * 128, 26 * 26 * 128};
-    uint32_t box[4] = {32, 8, 8, 1};
+    uint32_t box[4] = {32, 10, 8, 2};     // 10-wide halo, 8 rows, the two images of a pair
     if (tc::make_tmap(&tmA, a1, 4, dims, str, box)) return -2;
     uint64_t wd[2] = {64, 288};
     uint64_t ws[1] = {256};
@@ -200,10 +217,10 @@ extern "C" int hvd_conv2_fprop(const float* a1, const float* w2, const float* bi
     attr = true;
   }
   Params p;
-  p.B = B; p.n_tiles = (B * 9 + 1) / 2; p.training = training; p.keep = keep; p.bias = bias2; p.p2 = p2; p.mask = mask;
+  p.B = B; p.n_tiles = ((B + 1) / 2) * 9; p.training = training; p.keep = keep; p.bias = bias2; p.p2 = p2; p.mask = mask;
   p.st = reinterpret_cast<const mnist::StepState*>(step_state);
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
-  conv2_fprop_kernel<<<ctas, 256, SMEM_BYTES, (cudaStream_t)stream>>>(tmA, tmW, p);
+  conv2_fprop_kernel<<<ctas, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(tmA, tmW, p);
   return (int)cudaGetLastError();
 }
