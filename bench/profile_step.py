@@ -43,7 +43,7 @@ def main():
     lib, s = e.lib, e._s()
     P, G = e._p, e._g
     res = {}
-    res["conv1_fwd"] = timeit(lambda: lib.hvd_conv1_fwd(e.x_in.data_ptr(), P("c1", "kernel").data_ptr(), P("c1", "bias").data_ptr(), e.a1.data_ptr(), 128, s))
+    res["conv1_fwd"] = timeit(lambda: lib.hvd_conv1_fwd(e.x_in.data_ptr(), P("c1", "kernel").data_ptr(), P("c1", "bias").data_ptr(), e.a1.data_ptr(), 128, None, 0, None, 0, e.state.data_ptr(), 0, s))
     res["conv2_fprop"] = timeit(lambda: lib.hvd_conv2_fprop(e.a1.data_ptr(), P("c2", "kernel").data_ptr(), P("c2", "bias").data_ptr(), e.p2.data_ptr(), e.mask2.data_ptr(), e.state.data_ptr(), 128, 1, e.keep1, 0, s))
     for ks in (24, 48, 96, 144):
         res[f"dense1_fwd_ks{ks}"] = timeit(lambda: tc_gemm(e.p2, P("f1", "kernel"), 128, 128, 9216, False, True, 128, ks, EPI_ATOMIC_ADD, out=e.h_pre, stream=s))

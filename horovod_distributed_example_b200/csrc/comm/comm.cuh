@@ -48,8 +48,10 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // Coherent 16-byte peer load / store (bypass the non-coherent L1 for remote data).
 __device__ __forceinline__ float4 ld_sys_f4(const float* p) {
   float4 v;
+  // no "memory" clobber: ordering against the barriers comes from their own fences, and leaving it
+  // out lets the compiler keep many of these in flight
   asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
 }
 __device__ __forceinline__ float4 ld_f4(const float* p) { return *reinterpret_cast<const float4*>(p); }
@@ -61,7 +63,7 @@ __device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
 __device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
   float4 v;
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc));
   return v;
 }
 __device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {

@@ -56,18 +56,11 @@ __device__ __forceinline__ float update_one(float g, float p, float& s0, float& 
 }
 
 template <int KIND>
-__device__ __forceinline__ float4 update_f4(float4 g, float* p_ptr, float* s0_ptr, float* s1_ptr,
-                                            const float* __restrict__ h) {
-  float4 p = *reinterpret_cast<float4*>(p_ptr);
-  float4 s0 = *reinterpret_cast<float4*>(s0_ptr);
-  float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (KIND != HVD_KIND_SGD) s1 = *reinterpret_cast<float4*>(s1_ptr);
+__device__ __forceinline__ float4 update_f4(float4 g, float4 p, float4& s0, float4& s1, const float* __restrict__ h) {
   p.x = update_one<KIND>(g.x, p.x, s0.x, s1.x, h);
   p.y = update_one<KIND>(g.y, p.y, s0.y, s1.y, h);
   p.z = update_one<KIND>(g.z, p.z, s0.z, s1.z, h);
   p.w = update_one<KIND>(g.w, p.w, s0.w, s1.w, h);
-  *reinterpret_cast<float4*>(s0_ptr) = s0;
-  if (KIND != HVD_KIND_SGD) *reinterpret_cast<float4*>(s1_ptr) = s1;
   return p;
 }
 
@@ -101,6 +94,20 @@ __global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedAr
 
   for (long long i = i0 + threadIdx.x; i < i1; i += (long long)blockDim.x * kUnroll) {
     float4 acc[kUnroll];
+    // local parameter/state loads are issued FIRST so they overlap the (much slower) peer loads
+    float4 pv[kUnroll], s0v[kUnroll], s1v[kUnroll];
+    if (KIND != HVD_KIND_NONE) {
+#pragma unroll
+      for (int u = 0; u < kUnroll; u++) {
+        const long long idx = i + (long long)u * blockDim.x;
+        if (idx < i1) {
+          const long long el = s + idx * 4;
+          pv[u] = ld_f4(mine + a.param_off + el);
+          s0v[u] = ld_f4(mine + a.slot0_off + el);
+          if (KIND != HVD_KIND_SGD) s1v[u] = ld_f4(mine + a.slot1_off + el);
+        }
+      }
+    }
     if (VARIANT == HVD_NVLS) {
 #pragma unroll
       for (int u = 0; u < kUnroll; u++) {
@@ -137,7 +144,9 @@ __global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedAr
       long long dst_off;
       if (KIND == HVD_KIND_NONE) { res = g; dst_off = a.out_off + el; }
       else {
-        res = update_f4<KIND>(g, mine + a.param_off + el, mine + a.slot0_off + el, mine + a.slot1_off + el, hloc);
+        res = update_f4<KIND>(g, pv[u], s0v[u], s1v[u], hloc);
+        *reinterpret_cast<float4*>(mine + a.slot0_off + el) = s0v[u];
+        if (KIND != HVD_KIND_SGD) *reinterpret_cast<float4*>(mine + a.slot1_off + el) = s1v[u];
         dst_off = a.param_off + el;
       }
       if (VARIANT == HVD_ONESHOT) {

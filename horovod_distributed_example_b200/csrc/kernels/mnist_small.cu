@@ -13,9 +13,30 @@ using namespace mnist;
 
 // ------------------------------------------------------------------------------- conv1 forward
 // One thread = one output pixel x 8 channels; the 9 taps come from L1, the 288 weights from smem.
+// It is also the step prologue: it zeroes the gradient ranges later kernels accumulate into with
+// red.add, clears the per-step loss/accuracy words and advances the dropout step counter, so the
+// captured graph needs no memset nodes.
+struct Conv1Prologue {
+  float* zero_a; int n_a;       // float4-aligned ranges to clear (may be null / 0)
+  float* zero_b; int n_b;
+  StepState* st;                // may be null
+  int advance_step;
+};
+
 __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[9][32]*/,
-                                                        const float* __restrict__ bias, float* __restrict__ a1, int B) {
+                                                        const float* __restrict__ bias, float* __restrict__ a1, int B,
+                                                        Conv1Prologue pro) {
   __shared__ float sw[9 * 32 + 32];
+  {
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    for (int i = gid; i < pro.n_a / 4; i += gsz) reinterpret_cast<float4*>(pro.zero_a)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = gid; i < pro.n_b / 4; i += gsz) reinterpret_cast<float4*>(pro.zero_b)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (gid == 0 && pro.st) {
+      pro.st->last_loss = 0.f;
+      pro.st->last_correct = 0.f;
+      if (pro.advance_step) pro.st->step += 1;
+    }
+  }
   for (int i = threadIdx.x; i < 9 * 32 + 32; i += blockDim.x) sw[i] = i < 288 ? w[i] : bias[i - 288];
   __syncthreads();
   const long long total = (long long)B * H1 * H1 * 4;
@@ -46,7 +67,7 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
 
 // ------------------------------------------------------------------------------- head
 struct HeadParams {
-  int B, training, backward;
+  int B, training, backward, rows_per_cta;
   float keep;
   float* h_pre;               // [B,128] split-K sums of dense1 (zeroed again after use)
   const float* b1;            // dense1 bias [128]
@@ -54,127 +75,127 @@ struct HeadParams {
   const float* b2;            // [10]
   const long long* labels;    // [B] int64 class ids
   float* dh_pre;              // [B,128] out: gradient wrt dense1 pre-activation
-  float* g_w2; float* g_b2; float* g_b1;   // gradient slots in the arena
+  float* g_w2; float* g_b2; float* g_b1;   // gradient slots in the arena (accumulated: zeroed by the prologue)
   float* probs;               // [B,10] out (predict / eval), may be null
   StepState* st;
 };
 
-// Single CTA, 1024 threads; everything lives in shared memory (h: 64 KB).
-__global__ void __launch_bounds__(1024, 1) head_kernel(HeadParams p) {
-  extern __shared__ float sm[];
-  float* h = sm;                        // [B][128] post relu+dropout activations
-  float* msk = h + p.B * HID;           // [B][128] d(h)/d(pre): 0 or 1/keep
-  float* w2 = msk + p.B * HID;          // [128][10]
-  float* dl = w2 + HID * NCLS;          // [B][10] logits -> probs -> dlogits
-  float* red = dl + p.B * NCLS;         // [64] scratch
-  const int tid = threadIdx.x, nt = blockDim.x;
+constexpr int HEAD_ROWS = 8;  // batch rows per CTA: one warp per row
+
+// Grid of ceil(B/8) CTAs x 256 threads; warp w owns batch row 8*cta + w.  Cross-row sums (dW2, db2,
+// db1, loss, accuracy) leave each CTA as one red.add per output.
+__global__ void __launch_bounds__(256) head_kernel(HeadParams p) {
+  __shared__ float h[HEAD_ROWS][HID];      // post relu+dropout activations
+  __shared__ float msk[HEAD_ROWS][HID];    // d(h)/d(pre): 0 or 1/keep
+  __shared__ float w2[HID * NCLS];
+  __shared__ float dl[HEAD_ROWS][NCLS + 2];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = blockIdx.x * HEAD_ROWS + warp;
+  const bool valid = row < p.B;
   const unsigned step = p.st->step, seed = p.st->seed;
   const float inv_keep = 1.0f / p.keep;
 
-  for (int i = tid; i < HID * NCLS; i += nt) w2[i] = p.w2[i];
-  for (int i4 = tid; i4 < p.B * HID / 4; i4 += nt) {
-    float4 v = reinterpret_cast<float4*>(p.h_pre)[i4];
-    reinterpret_cast<float4*>(p.h_pre)[i4] = make_float4(0.f, 0.f, 0.f, 0.f);   // re-arm the split-K accumulator
-    const int j = (i4 * 4) & (HID - 1);
+  for (int i = tid; i < HID * NCLS; i += 256) w2[i] = __ldg(p.w2 + i);
+  {
+    // lane owns hidden units 4*lane .. 4*lane+3 of its row
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid) {
+      float4* src = reinterpret_cast<float4*>(p.h_pre + (long long)row * HID) + lane;
+      v = *src;
+      *src = make_float4(0.f, 0.f, 0.f, 0.f);                  // re-arm the split-K accumulator
+    }
+    const float4 bb = __ldg(reinterpret_cast<const float4*>(p.b1) + lane);
     uint4 rnd = make_uint4(0, 0, 0, 0);
-    if (p.training) rnd = philox4x32_10(make_uint4((unsigned)i4, step, 0x1u, 0u), make_uint2(seed, 0x5EEDu));
-    const float pre[4] = {v.x + p.b1[j], v.y + p.b1[j + 1], v.z + p.b1[j + 2], v.w + p.b1[j + 3]};
+    if (p.training) rnd = philox4x32_10(make_uint4((unsigned)(row * (HID / 4) + lane), step, 0x1u, 0u), make_uint2(seed, 0x5EEDu));
+    const float pre[4] = {v.x + bb.x, v.y + bb.y, v.z + bb.z, v.w + bb.w};
     const unsigned rr[4] = {rnd.x, rnd.y, rnd.z, rnd.w};
+    const float scale = p.training ? inv_keep : 1.0f;
 #pragma unroll
     for (int e = 0; e < 4; e++) {
-      const bool keep = !p.training || u01(rr[e]) < p.keep;
-      const float scale = p.training ? inv_keep : 1.0f;
-      const bool live = keep && pre[e] > 0.f;
-      h[i4 * 4 + e] = live ? pre[e] * scale : 0.f;
-      msk[i4 * 4 + e] = live ? scale : 0.f;
+      const bool live = valid && (!p.training || u01(rr[e]) < p.keep) && pre[e] > 0.f;
+      h[warp][lane * 4 + e] = live ? pre[e] * scale : 0.f;
+      msk[warp][lane * 4 + e] = live ? scale : 0.f;
     }
   }
   __syncthreads();
-  // logits[b][k]
-  for (int o = tid; o < p.B * NCLS; o += nt) {
-    const int b = o / NCLS, k = o % NCLS;
-    float acc = p.b2[k];
-    const float* hb = h + b * HID;
-#pragma unroll 8
-    for (int j = 0; j < HID; j++) acc = fmaf(hb[j], w2[j * NCLS + k], acc);
-    dl[o] = acc;
+  // logits: each lane does its 4 hidden units for all 10 classes, then a warp all-reduce
+  float lg[NCLS];
+#pragma unroll
+  for (int k = 0; k < NCLS; k++) lg[k] = 0.f;
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    const float hv = h[warp][lane * 4 + e];
+#pragma unroll
+    for (int k = 0; k < NCLS; k++) lg[k] = fmaf(hv, w2[(lane * 4 + e) * NCLS + k], lg[k]);
   }
-  __syncthreads();
-  // softmax, loss, accuracy, dlogits: one thread per sample
-  float my_loss = 0.f, my_ok = 0.f;
-  if (tid < p.B) {
-    float* l = dl + tid * NCLS;
-    float mx = l[0];
-    int am = 0;
 #pragma unroll
-    for (int k = 1; k < NCLS; k++) if (l[k] > mx) { mx = l[k]; am = k; }
-    float e[NCLS], s = 0.f;
+  for (int k = 0; k < NCLS; k++) {
 #pragma unroll
-    for (int k = 0; k < NCLS; k++) { e[k] = expf(l[k] - mx); s += e[k]; }
-    const int y = (int)p.labels[tid];
-    const float inv = 1.0f / s;
-    const float py = fminf(fmaxf(e[y] * inv, 1e-7f), 1.0f - 1e-7f);     // Keras clips probabilities
-    my_loss = -logf(py);
-    my_ok = (am == y) ? 1.f : 0.f;
-    const float invB = 1.0f / (float)p.B;
+    for (int o = 16; o > 0; o >>= 1) lg[k] += __shfl_xor_sync(0xffffffffu, lg[k], o);
+    lg[k] += __ldg(p.b2 + k);
+  }
+  // softmax / loss / accuracy (every lane holds the row's 10 logits)
+  float mx = lg[0];
+  int am = 0;
 #pragma unroll
-    for (int k = 0; k < NCLS; k++) {
-      const float pk = e[k] * inv;
-      if (p.probs) p.probs[tid * NCLS + k] = pk;
-      l[k] = (pk - (k == y ? 1.f : 0.f)) * invB;
+  for (int k = 1; k < NCLS; k++) if (lg[k] > mx) { mx = lg[k]; am = k; }
+  float e[NCLS], ssum = 0.f;
+#pragma unroll
+  for (int k = 0; k < NCLS; k++) { e[k] = expf(lg[k] - mx); ssum += e[k]; }
+  const int y = valid ? (int)p.labels[row] : 0;
+  const float inv = 1.0f / ssum, invB = 1.0f / (float)p.B;
+  float py = 0.f;
+#pragma unroll
+  for (int k = 0; k < NCLS; k++) {
+    const float pk = e[k] * inv;
+    if (k == y) py = pk;
+    if (lane == k) {
+      if (p.probs && valid) p.probs[(long long)row * NCLS + k] = pk;
+      dl[warp][k] = valid ? (pk - (k == y ? 1.f : 0.f)) * invB : 0.f;
     }
   }
-  // block reduction of loss / correct
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    my_loss += __shfl_xor_sync(0xffffffffu, my_loss, o);
-    my_ok += __shfl_xor_sync(0xffffffffu, my_ok, o);
+  if (lane == 0 && valid) {
+    const float loss = -logf(fminf(fmaxf(py, 1e-7f), 1.0f - 1e-7f));     // Keras clips probabilities
+    atomicAdd(&p.st->last_loss, p.backward ? loss * invB : loss);        // eval mode reports sums
+    atomicAdd(&p.st->last_correct, am == y ? 1.f : 0.f);
   }
-  if ((tid & 31) == 0) { red[tid >> 5] = my_loss; red[32 + (tid >> 5)] = my_ok; }
   __syncthreads();
-  if (tid == 0) {
-    float ls = 0.f, ok = 0.f;
-    for (int i = 0; i < nt / 32; i++) { ls += red[i]; ok += red[32 + i]; }
-    const float mean = ls / (float)p.B;
-    p.st->last_loss = p.backward ? mean : ls;      // eval mode reports sums (weighted by batch size)
-    p.st->last_correct = ok;
-    p.st->loss_sum += mean;
-    p.st->correct_sum += ok;
-    if (p.backward) p.st->step = step + 1;
-  }
   if (!p.backward) return;
-  // dW2[j][k] = sum_b h[b][j] dl[b][k];  db2[k] = sum_b dl[b][k]
-  for (int o = tid; o < HID * NCLS + NCLS; o += nt) {
+  // dW2[j][k] += sum_rows h[r][j] dl[r][k];  db2[k] += sum_rows dl[r][k]
+  for (int o = tid; o < HID * NCLS + NCLS; o += 256) {
     float acc = 0.f;
     if (o < HID * NCLS) {
       const int j = o / NCLS, k = o % NCLS;
-#pragma unroll 8
-      for (int b = 0; b < p.B; b++) acc = fmaf(h[b * HID + j], dl[b * NCLS + k], acc);
-      p.g_w2[o] = acc;
+#pragma unroll
+      for (int r = 0; r < HEAD_ROWS; r++) acc = fmaf(h[r][j], dl[r][k], acc);
+      atomicAdd(p.g_w2 + o, acc);
     } else {
       const int k = o - HID * NCLS;
-#pragma unroll 8
-      for (int b = 0; b < p.B; b++) acc += dl[b * NCLS + k];
-      p.g_b2[k] = acc;
+#pragma unroll
+      for (int r = 0; r < HEAD_ROWS; r++) acc += dl[r][k];
+      atomicAdd(p.g_b2 + k, acc);
     }
   }
-  __syncthreads();                       // dW2 above still reads h; the loop below overwrites it
-  // dh_pre[b][j] = (sum_k dl[b][k] w2[j][k]) * mask;   db1[j] = sum_b dh_pre[b][j]
-  for (int o = tid; o < p.B * HID; o += nt) {
-    const int b = o / HID, j = o % HID;
+  // dh_pre[row][j] = (sum_k dl[row][k] w2[j][k]) * mask;   db1[j] += sum_rows dh_pre[row][j]
+  float dh[4];
+#pragma unroll
+  for (int e4 = 0; e4 < 4; e4++) {
+    const int j = lane * 4 + e4;
     float acc = 0.f;
 #pragma unroll
-    for (int k = 0; k < NCLS; k++) acc = fmaf(dl[b * NCLS + k], w2[j * NCLS + k], acc);
-    acc *= msk[o];
-    p.dh_pre[o] = acc;
-    h[o] = acc;                          // reuse h for the column sums below
+    for (int k = 0; k < NCLS; k++) acc = fmaf(dl[warp][k], w2[j * NCLS + k], acc);
+    dh[e4] = acc * msk[warp][j];
   }
+  if (valid) reinterpret_cast<float4*>(p.dh_pre + (long long)row * HID)[lane] = make_float4(dh[0], dh[1], dh[2], dh[3]);
+  __syncthreads();                         // everyone is done reading h: reuse it for the column sums
+#pragma unroll
+  for (int e4 = 0; e4 < 4; e4++) h[warp][lane * 4 + e4] = dh[e4];
   __syncthreads();
-  for (int j = tid; j < HID; j += nt) {
+  if (tid < HID) {
     float acc = 0.f;
-#pragma unroll 8
-    for (int b = 0; b < p.B; b++) acc += h[b * HID + j];
-    p.g_b1[j] = acc;
+#pragma unroll
+    for (int r = 0; r < HEAD_ROWS; r++) acc += h[r][tid];
+    atomicAdd(p.g_b1 + tid, acc);
   }
 }
 
@@ -188,16 +209,27 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
   float acc[10];
 #pragma unroll
   for (int k = 0; k < 10; k++) acc[k] = 0.f;
-  for (long long pix = (long long)blockIdx.x * 8 + warp; pix < npix; pix += (long long)gridDim.x * 8) {
-    const int ox = (int)(pix % H1), oy = (int)((pix / H1) % H1);
-    const int b = (int)(pix / (H1 * H1));
-    const float g = da1[pix * C1 + lane];
-    const float* xi = x + ((long long)b * IMG + oy) * IMG + ox;
+  constexpr int U = 4;                      // pixels in flight per warp (memory-level parallelism)
+  for (long long pix0 = ((long long)blockIdx.x * 8 + warp) * U; pix0 < npix; pix0 += (long long)gridDim.x * 8 * U) {
+    float g[U], xv[U][9];
 #pragma unroll
-    for (int kh = 0; kh < 3; kh++)
+    for (int u = 0; u < U; u++) {
+      const long long pix = pix0 + u < npix ? pix0 + u : npix - 1;
+      const int ox = (int)(pix % H1), oy = (int)((pix / H1) % H1);
+      const int b = (int)(pix / (H1 * H1));
+      g[u] = pix0 + u < npix ? __ldg(da1 + pix * C1 + lane) : 0.f;
+      const float* xi = x + ((long long)b * IMG + oy) * IMG + ox;
 #pragma unroll
-      for (int kw = 0; kw < 3; kw++) acc[kh * 3 + kw] = fmaf(__ldg(xi + kh * IMG + kw), g, acc[kh * 3 + kw]);
-    acc[9] += g;
+      for (int kh = 0; kh < 3; kh++)
+#pragma unroll
+        for (int kw = 0; kw < 3; kw++) xv[u][kh * 3 + kw] = __ldg(xi + kh * IMG + kw);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+#pragma unroll
+      for (int k = 0; k < 9; k++) acc[k] = fmaf(xv[u][k], g[u], acc[k]);
+      acc[9] += g[u];
+    }
   }
 #pragma unroll
   for (int k = 0; k < 10; k++) red[warp][k][lane] = acc[k];
@@ -225,27 +257,24 @@ __global__ void __launch_bounds__(256) colsum64_kernel(const float* __restrict__
 
 }  // namespace
 
-extern "C" int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, void* stream) {
+extern "C" int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a,
+                             int n_a, float* zero_b, int n_b, void* step_state, int advance_step, void* stream) {
+  if ((n_a | n_b) & 3) return -1;
   const long long total = (long long)B * mnist::H1 * mnist::H1 * 4;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  conv1_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, w, bias, a1, B);
+  Conv1Prologue pro{zero_a, zero_a ? n_a : 0, zero_b, zero_b ? n_b : 0, reinterpret_cast<mnist::StepState*>(step_state), advance_step};
+  conv1_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, w, bias, a1, B, pro);
   return (int)cudaGetLastError();
 }
 
 extern "C" int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels,
                         float* dh_pre, float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B,
                         int training, int backward, float keep, void* stream) {
-  if (B > 256 || (B * mnist::HID) % 4) return -1;
-  HeadParams p{B, training, backward, keep, h_pre, b1, w2, b2, labels, dh_pre, g_w2, g_b2, g_b1, probs,
+  if (B < 1) return -1;
+  HeadParams p{B, training, backward, HEAD_ROWS, keep, h_pre, b1, w2, b2, labels, dh_pre, g_w2, g_b2, g_b1, probs,
                reinterpret_cast<mnist::StepState*>(step_state)};
-  const int smem = (2 * B * mnist::HID + mnist::HID * mnist::NCLS + B * mnist::NCLS + 64) * 4;
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    if (cudaFuncSetAttribute(head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -10;
-    attr_smem = smem;
-  }
-  head_kernel<<<1, 1024, smem, (cudaStream_t)stream>>>(p);
+  head_kernel<<<(B + HEAD_ROWS - 1) / HEAD_ROWS, 256, 0, (cudaStream_t)stream>>>(p);
   return (int)cudaGetLastError();
 }
 

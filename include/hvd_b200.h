@@ -106,9 +106,14 @@ int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, i
                 unsigned lbo_b, unsigned sbo_b, const uint8_t* mask, float scale);
 
 /* Fused MNIST-CNN engine kernels (reference model mnist_keras.py:71-81). */
-int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, void* stream);
+/* conv1 forward; also the step prologue: clears [zero_a, +n_a) and [zero_b, +n_b) (the gradient ranges
+ * later kernels red.add into; multiples of 4 floats, may be NULL), clears the per-step loss/accuracy words
+ * of step_state and, if advance_step, bumps its dropout step counter. */
+int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a, int n_a,
+                  float* zero_b, int n_b, void* step_state, int advance_step, void* stream);
 int hvd_conv2_fprop(const float* a1, const float* w2, const float* bias2, float* p2, uint8_t* mask,
                     const void* step_state, int B, int training, float keep, int ctas, void* stream);
+/* g_w2 / g_b2 / g_b1 and the loss/accuracy words are ACCUMULATED into (zeroed by hvd_conv1_fwd's prologue). */
 int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels, float* dh_pre,
              float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B, int training, int backward,
              float keep, void* stream);
