@@ -1,0 +1,113 @@
+"""ResNet-50 large-bucket stress (BASELINE.json config 5): synthetic ImageNet-shape batches through the
+same DistributedOptimizer - arena, static bucket plan, fused peer-memory allreduce+update kernels
+overlapped with backward by per-bucket hooks - against torch DDP (bucketed NCCL, overlapped) on the
+same model.  Model compute is stock torch/cuDNN in both arms; the difference is the optimizer path.
+
+    torchrun --nproc-per-node N bench/resnet50_stress.py [--impl ours|ddp] [--batch 32] [--steps 30]
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+
+
+def run_ours(a):
+    import horovod_distributed_example_b200 as hvd
+    from horovod_distributed_example_b200 import keras
+    from horovod_distributed_example_b200.models.resnet import resnet50
+    hvd.init()
+    n = hvd.size()
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.benchmark = True
+    torch.manual_seed(0)
+    net = resnet50().to(memory_format=torch.channels_last)
+    m = keras.TorchModel(net, channels_last_input=True)
+    opt = hvd.DistributedOptimizer(keras.optimizers.SGD(0.0125 * n, momentum=0.9))
+    m.compile(optimizer=opt, loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True))
+    x = torch.randn(a.batch, 224, 224, 3, device="cuda")
+    y = torch.randint(0, 1000, (a.batch,), device="cuda")
+    m._ensure_built((a.batch, 224, 224, 3))
+    hvd.broadcast_global_variables(0, m)
+    be = m._backend
+    for _ in range(a.warmup):
+        be.train_step(x, y)
+    torch.cuda.synchronize()
+    hvd.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        loss, _ = be.train_step(x, y)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = float(hvd.allgather(torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64)).max())
+    cs = hvd.allgather_object(int(m.arena.checksum()))
+    if hvd.rank() == 0:
+        f = getattr(opt, "_fused", None)
+        print(json.dumps({"impl": "ours", "n_gpus": n, "batch_per_gpu": a.batch, "images_per_sec": a.batch * n * a.steps / (ms / 1e3),
+                          "ms_per_step": ms / a.steps, "params": m.arena.n_params(), "grad_bytes": m.arena.n_params() * 4,
+                          "tensors": len(m.arena.specs), "buckets": f.describe() if f else "torch/nccl",
+                          "overlap_hooks": bool(getattr(opt, "_hooked", False)),
+                          "replicas_bit_identical": all(c == cs[0] for c in cs), "loss": float(loss)}))
+    hvd.shutdown()
+
+
+def run_ddp(a):
+    import torch.distributed as dist
+    from horovod_distributed_example_b200.models.resnet import resnet50
+    rank, n, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(lr)
+    if n > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.benchmark = True
+    torch.manual_seed(0)
+    net = resnet50().cuda().to(memory_format=torch.channels_last)
+    model = torch.nn.parallel.DistributedDataParallel(net, device_ids=[lr], bucket_cap_mb=16, gradient_as_bucket_view=True) if n > 1 else net
+    opt = torch.optim.SGD(net.parameters(), lr=0.0125 * n, momentum=0.9)
+    x = torch.randn(a.batch, 3, 224, 224, device="cuda").to(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (a.batch,), device="cuda")
+
+    def step():
+        opt.zero_grad(set_to_none=False)
+        loss = torch.nn.functional.cross_entropy(model(x), y)
+        loss.backward()
+        opt.step()
+        return loss
+
+    for _ in range(a.warmup):
+        step()
+    torch.cuda.synchronize()
+    if n > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    if n > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(json.dumps({"impl": "torch_ddp", "n_gpus": n, "batch_per_gpu": a.batch,
+                          "images_per_sec": a.batch * n * a.steps / (float(ms) / 1e3), "ms_per_step": float(ms) / a.steps,
+                          "loss": float(loss)}))
+    if n > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--impl", default="ours", choices=["ours", "ddp"])
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=8)
+    a = ap.parse_args()
+    (run_ours if a.impl == "ours" else run_ddp)(a)

@@ -220,6 +220,9 @@ class Model:
         """One optimisation step on a host batch.  Returns ``[loss, accuracy]`` floats."""
         x, y = _to_numpy(x), _to_numpy(y)
         self._ensure_built(x.shape)
+        if hasattr(self._backend, "train_host_batch"):
+            loss, acc = self._backend.train_host_batch(x, y)     # direct H2D into the engine's buffers
+            return [loss, acc] if self._metric_accuracy else loss
         st = self._stager()
         xd, yd = st(x, torch.float32), st(y)
         st.next_step()
@@ -567,8 +570,11 @@ class _TorchBackend:
     def train_step(self, x, y):
         m = self.m
         arena = m.arena
-        arena.grads.zero_()
         opt = m.optimizer
+        if getattr(opt, "_hooked", False):
+            # a fused bucket kernel of the previous step may still be reading the gradient slab on the side stream
+            torch.cuda.current_stream(m.device).wait_stream(opt._fused.side_stream)
+        arena.grads.zero_()
         if hasattr(opt, "begin_step"):
             opt.begin_step()
         with torch.enable_grad():

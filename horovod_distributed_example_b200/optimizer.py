@@ -38,6 +38,7 @@ class _DistributedMixin:
         self._fused = None
         self._cut_after: List[str] = []
         self._pass = 0
+        self._hooked = False
 
     # -- plan -----------------------------------------------------------------------
     def bind(self, arena) -> None:
@@ -84,6 +85,52 @@ class _DistributedMixin:
 
     def begin_step(self) -> None:
         basics.state().step += 1
+        if self._hooked:
+            self._pending = list(self._bucket_size)
+            self._launched = [False] * len(self._buckets)
+
+    # -- backward overlap for the torch-autograd backend ---------------------------------------
+    def attach_model(self, model) -> None:
+        """Overlap communication with backward (what Horovod gets from its background thread and DDP
+        from its reducer): a post-accumulate-grad hook per parameter counts down its bucket; the
+        moment a bucket's last gradient lands, its fused allreduce+update kernel is launched on a
+        side stream behind an event, while autograd keeps producing the earlier layers' gradients."""
+        self._hooked = False
+        if self._fused is None or len(self._buckets) < 2 or getattr(model, "_named", None) is None:
+            return
+        arena = self._arena
+        index = {s.name: i for i, s in enumerate(arena.specs)}
+        owner = {}
+        for b in self._buckets:
+            for t in range(b.first_tensor, b.last_tensor + 1):
+                owner[t] = b.index
+        self._bucket_size = [b.last_tensor - b.first_tensor + 1 for b in self._buckets]
+        self._pending = list(self._bucket_size)
+        self._launched = [False] * len(self._buckets)
+        for h in getattr(self, "_hook_handles", []):
+            h.remove()
+        self._hook_handles = []
+        for name, p in model._named:
+            bi = owner[index[name]]
+            self._hook_handles.append(p.register_post_accumulate_grad_hook(self._make_hook(bi)))
+        self._hooked = True
+
+    def _make_hook(self, bi: int):
+        def hook(_param):
+            self._pending[bi] -= 1
+            if self._pending[bi] == 0 and self._pass % self._bpps == self._bpps - 1:
+                self._launch_bucket(bi)
+        return hook
+
+    def _launch_bucket(self, bi: int) -> None:
+        if self._launched[bi]:
+            return
+        self._launched[bi] = True
+        f = self._fused
+        ev = f._events[bi]
+        ev.record(torch.cuda.current_stream(self._arena.device))
+        f.side_stream.wait_event(ev)
+        f.run_bucket(bi, 0, 1, stream=f.side_stream)
 
     def apply_gradients(self, arena=None) -> None:
         arena = arena or self._arena
@@ -93,7 +140,12 @@ class _DistributedMixin:
         if self._fused is not None and self._compression is Compression.none:
             # fused peer-memory path: reduce + scale + update in one kernel per bucket
             self.iterations += 1
-            self._fused.run_all()
+            if self._hooked:
+                for bi in range(len(self._buckets)):      # anything the hooks did not launch (unused params)
+                    self._launch_bucket(bi)
+                torch.cuda.current_stream(arena.device).wait_stream(self._fused.side_stream)
+            else:
+                self._fused.run_all()
             self._push_hyper()
             cfg = basics.config()
             if cfg.debug_checksum and self.iterations % cfg.debug_checksum == 0:

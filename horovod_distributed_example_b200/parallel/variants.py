@@ -49,7 +49,8 @@ def reload():
 def default_ctas(nbytes: int, variant: int, nranks: int) -> int:
     """Enough CTAs to keep ~2 MB in flight on NVLink for large messages, one for tiny ones."""
     work = nbytes if variant == ONESHOT else max(nbytes // max(nranks, 1), 1)
-    return int(max(1, min(148, (work + 16383) // 16384)))      # <= one CTA per SM: always co-resident
+    cap = 32 if variant == NVLS else 148   # measured: multimem traffic peaks around 32 CTAs (profiles/allreduce_sweep_N8.json)
+    return int(max(1, min(cap, (work + 16383) // 16384)))      # <= one CTA per SM: always co-resident
 
 
 def pick(nbytes: int, nranks: int, has_nvls: bool, forced: str = "auto", forced_ctas: int = 0

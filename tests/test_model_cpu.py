@@ -101,3 +101,26 @@ def test_export_serving_artifacts(tmp_path, hvd_single):
     assert sorted(os.listdir(out)) == ["model.h5", "model.ts", "signature.json"]
     ts = torch.jit.load(os.path.join(out, "model.ts"))
     np.testing.assert_allclose(ts(torch.from_numpy(x)).numpy(), m.predict(x), rtol=1e-5, atol=1e-6)
+
+
+def test_torchmodel_resnet_tiny_trains_through_arena(hvd_single):
+    """Any nn.Module (here a tiny ResNet with BatchNorm and residuals) trains through the same arena /
+    DistributedOptimizer path: parameters are re-homed into the arena in reverse registration order."""
+    from horovod_distributed_example_b200.models.resnet import resnet_tiny
+    torch.manual_seed(0)
+    net = resnet_tiny(10)
+    n_params = sum(p.numel() for p in net.parameters())
+    m = keras.TorchModel(net)
+    m.compile(optimizer=hvd_single.DistributedOptimizer(O.SGD(0.05, momentum=0.9)),
+              loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True), metrics=["accuracy"])
+    rng = np.random.default_rng(0)
+    x = rng.random((32, 32, 32, 3), dtype=np.float32)
+    y = (x.mean(axis=(1, 2, 3)) > 0.5).astype(np.int64)
+    losses = [m.train_on_batch(x, y)[0] for _ in range(12)]
+    assert m.arena.n_params() == n_params and losses[-1] < losses[0]
+    assert m.arena.specs[0].name.startswith("fc.")                  # last layer first: backward-ready order
+    for name, p in net.named_parameters():
+        assert p.data_ptr() == m.arena.param(name).data_ptr()       # module weights ARE arena views
+    from horovod_distributed_example_b200.parallel import buckets as B
+    bk = B.plan(m.arena, 16 << 10)
+    assert len(bk) > 3 and bk[0].start == 0 and bk[-1].end == m.arena.n
