@@ -142,8 +142,9 @@ def init(comm=None, *, backend: Optional[str] = None, device: Optional[str] = No
         else:
             if dist.get_rank() != rank or dist.get_world_size() != size:
                 raise RuntimeError("torch.distributed is already initialised with a different world")
-        be = dist.get_backend()
-        if "gloo" in str(be):
+        # host-side control traffic (barriers, object exchange, fd bootstrap) always goes over a
+        # dedicated gloo group so it can never interleave with device collectives
+        if str(dist.get_backend()) == "gloo":
             _state.cpu_group = dist.group.WORLD
         else:
             _state.cpu_group = dist.new_group(backend="gloo")

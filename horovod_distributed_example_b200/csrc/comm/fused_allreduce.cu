@@ -266,4 +266,8 @@ extern "C" int hvd_can_access_peer(int dev, int peer) {
   if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) return -1;
   return ok;
 }
+// Plain device-to-device copy on `stream`; src may be a peer-mapped (VMM / IPC) address.
+extern "C" int hvd_memcpy_d2d(void* dst, const void* src, long long bytes, void* stream) {
+  return (int)cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+}
 extern "C" const char* hvd_cuda_error_string(int e) { return cudaGetErrorString((cudaError_t)e); }

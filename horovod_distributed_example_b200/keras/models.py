@@ -114,29 +114,28 @@ class Model:
 
     # ---- arena ----------------------------------------------------------------------
     def _make_arena(self, specs, inits, device, n_slots=0):
-        from .. import basics
-        allocator = None
-        double = False
-        if device.type == "cuda" and basics.is_initialized():
-            from ..parallel import peer
-            if peer.available():
-                allocator = peer.context().alloc_tensor
-                double = basics.size() > 1   # double-buffered grads drop the exit barrier
-        self.arena = ParamArena(specs, device, n_slots, double_grads=double, allocator=allocator)
+        # Always a plain local arena here: building a model is a rank-local act (the reference loads a
+        # model on rank 0 only, mnist_keras.py:124).  compile() with a DistributedOptimizer - which
+        # every rank executes - is what moves it into peer-mapped symmetric memory (a collective).
+        self.arena = ParamArena(specs, device, n_slots)
         g = torch.Generator().manual_seed(self._seed) if self._seed is not None else None
         with torch.no_grad():
             for (name, _shape), init in zip(specs, inits):
                 self.arena.param(name).copy_(init(g).to(torch.float32))
         self.device = device
 
-    def _ensure_slots(self, n_slots: int):
-        if self.arena.n_slots >= n_slots:
+    def _ensure_arena(self, n_slots: int, symmetric: bool):
+        """Re-home the arena when the optimizer needs more slots or symmetric (peer-mapped) memory."""
+        ar = self.arena
+        if ar.n_slots >= n_slots and (ar.symmetric or not symmetric):
             return
-        allocator = None
-        if self.arena.symmetric:
+        allocator, double = None, ar.n_grad_bufs == 2
+        if symmetric or ar.symmetric:
+            from .. import basics
             from ..parallel import peer
             allocator = peer.context().alloc_tensor
-        self.arena = self.arena.resize_slots(n_slots, allocator)
+            double = basics.size() > 1       # double-buffered grads drop the one-shot exit barrier (DESIGN.md)
+        self.arena = ar.resize_slots(max(n_slots, ar.n_slots), allocator, double_grads=double)
         self._rebind_weights()
 
     def _rebind_weights(self): raise NotImplementedError
@@ -162,7 +161,12 @@ class Model:
             self._finish_compile()
 
     def _finish_compile(self):
-        self._ensure_slots(self.optimizer.n_slots)
+        from .. import basics
+        want_symm = False
+        if self.device.type == "cuda" and basics.is_initialized() and getattr(self.optimizer, "_hvd_distributed", False):
+            from ..parallel import peer
+            want_symm = peer.available()
+        self._ensure_arena(self.optimizer.n_slots, want_symm)
         self.optimizer.bind(self.arena)
         if hasattr(self.optimizer, "attach_model"):
             self.optimizer.attach_model(self)

@@ -133,10 +133,13 @@ class ParamArena:
         idx = torch.arange(1, w.numel() + 1, device=w.device, dtype=torch.int64)
         return ((w * (idx % 8191 + 1)).sum()) & 0x7FFFFFFFFFFF
 
-    def resize_slots(self, n_slots: int, allocator=None) -> "ParamArena":
-        """Return a new arena with ``n_slots`` optimizer slots, carrying params over."""
+    def resize_slots(self, n_slots: int, allocator=None, double_grads: Optional[bool] = None) -> "ParamArena":
+        """Return a new arena with ``n_slots`` optimizer slots (optionally in memory from ``allocator``),
+        carrying params and existing slots over."""
+        if double_grads is None:
+            double_grads = self.n_grad_bufs == 2
         new = ParamArena([(s.name, s.shape) for s in self.specs], self.device, n_slots,
-                         double_grads=self.n_grad_bufs == 2, allocator=allocator)
+                         double_grads=double_grads, allocator=allocator)
         new.params.copy_(self.params)
         for i in range(min(n_slots, self.n_slots)):
             new.slots[i].copy_(self.slots[i])

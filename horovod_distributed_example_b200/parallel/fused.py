@@ -91,8 +91,7 @@ class FusedReducer:
                 s, e = self.shard_range(i, r)
                 if e <= s:
                     continue
-                remote = self.buf.peer_tensor(r)
                 for k in range(ar.n_slots):
                     o = self.base_off + ar.slot_offset(k)
-                    self.buf.tensor[o + s:o + e].copy_(remote[o + s:o + e])
+                    self.ctx.pull(self.buf, r, o + s, e - s)
         torch.cuda.synchronize(ar.device)

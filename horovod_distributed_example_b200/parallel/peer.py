@@ -114,6 +114,8 @@ def _declare(lib):
     lib.hvd_ipc_close.argtypes = [ctypes.c_void_p]
     lib.hvd_cuda_error_string.restype = ctypes.c_char_p
     lib.hvd_cuda_error_string.argtypes = [ctypes.c_int]
+    lib.hvd_memcpy_d2d.restype = ctypes.c_int
+    lib.hvd_memcpy_d2d.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p]
     lib.hvd_pad_bytes.restype = ctypes.c_int
     lib.hvd_epoch_bytes.restype = ctypes.c_int
     lib._hvd_comm_declared = True
@@ -426,6 +428,15 @@ class PeerContext:
                                        self._stream(stream), self.size if self.emulated else 0)
         if rc != 0:
             raise RuntimeError(f"hvd_bcast_launch failed: {rc}")
+
+    def pull(self, buf: SymmBuffer, src_rank: int, elem_off: int, n_elems: int, stream=None) -> None:
+        """One-sided read: copy [elem_off, elem_off+n) of rank ``src_rank``'s copy of ``buf`` into this
+        rank's copy (cudaMemcpyAsync on the peer-mapped address; torch never sees the peer pointer)."""
+        dst = buf.ptrs[buf.local_index] + 4 * elem_off
+        src = buf.ptrs[src_rank] + 4 * elem_off
+        rc = self.lib.hvd_memcpy_d2d(dst, src, 4 * n_elems, self._stream(stream))
+        if rc != 0:
+            raise RuntimeError(f"peer pull failed: {self.lib.hvd_cuda_error_string(rc).decode()}")
 
     def check_error(self) -> None:
         """Raise if an in-kernel barrier timed out (names the peer that did not arrive)."""

@@ -96,6 +96,7 @@ int hvd_ipc_get_handle(void* p, void* out64);
 int hvd_ipc_open(const void* h64, void** p);
 int hvd_ipc_close(void* p);
 int hvd_can_access_peer(int dev, int peer);
+int hvd_memcpy_d2d(void* dst, const void* src, long long bytes, void* stream);
 const char* hvd_cuda_error_string(int e);
 
 /* tcgen05 TF32 GEMM, D[M,N] = A*B.  A: [M][K] (a_mn=0) or [K][M] (a_mn=1); B: [N][K] or [K][N].
