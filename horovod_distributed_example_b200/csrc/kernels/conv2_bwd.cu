@@ -68,6 +68,8 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
 
   if (warp == 0) {
     if (tc::elect_one()) {
@@ -200,6 +202,8 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
 
   if (warp == 0) {
     if (tc::elect_one()) {
@@ -287,8 +291,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
   dg::Params p{B, B * 8, a1, da1};
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
-  dg::conv2_dgrad_kernel<<<ctas, 256, dg::SMEM_BYTES, (cudaStream_t)stream>>>(tmG, tmW, p);
-  return (int)cudaGetLastError();
+  return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(256), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);
 }
 
 // g_w / g_b are ACCUMULATED into (red.add): the caller zeroes them before the step.
@@ -315,6 +318,5 @@ extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, fl
   p.patches_per_cta = (p.n_patches + ctas - 1) / ctas;
   ctas = (p.n_patches + p.patches_per_cta - 1) / p.patches_per_cta;
   p.g_w = g_w; p.g_b = g_b;
-  wg::conv2_wgrad_kernel<<<ctas, 256, wg::SMEM_BYTES, (cudaStream_t)stream>>>(tmA, tmG, p);
-  return (int)cudaGetLastError();
+  return (int)tc::launch_pdl(wg::conv2_wgrad_kernel, dim3(ctas), dim3(256), wg::SMEM_BYTES, (cudaStream_t)stream, tmA, tmG, p);
 }

@@ -69,6 +69,8 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
 
   if (warp == 0) {
     if (tc::elect_one()) {
@@ -221,6 +223,5 @@ extern "C" int hvd_conv2_fprop(const float* a1, const float* w2, const float* bi
   p.st = reinterpret_cast<const mnist::StepState*>(step_state);
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
-  conv2_fprop_kernel<<<ctas, THREADS, SMEM_BYTES, (cudaStream_t)stream>>>(tmA, tmW, p);
-  return (int)cudaGetLastError();
+  return (int)tc::launch_pdl(conv2_fprop_kernel, dim3(ctas), dim3(THREADS), SMEM_BYTES, (cudaStream_t)stream, tmA, tmW, p);
 }

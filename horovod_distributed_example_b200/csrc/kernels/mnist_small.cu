@@ -7,6 +7,7 @@
 //                                                                          (mnist_keras.py:79-81,89-91)
 //   conv1_wgrad : dW/db of conv1 and db of conv2 (pure reductions)
 #include "mnist_common.cuh"
+#include "tc_common.cuh"
 
 namespace {
 using namespace mnist;
@@ -27,6 +28,8 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
                                                         const float* __restrict__ bias, float* __restrict__ a1, int B,
                                                         Conv1Prologue pro) {
   __shared__ float sw[9 * 32 + 32];
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
   {
     const int gid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
     for (int i = gid; i < pro.n_a / 4; i += gsz) reinterpret_cast<float4*>(pro.zero_a)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -92,6 +95,8 @@ __global__ void __launch_bounds__(256) head_kernel(HeadParams p) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int row = blockIdx.x * HEAD_ROWS + warp;
   const bool valid = row < p.B;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
   const unsigned step = p.st->step, seed = p.st->seed;
   const float inv_keep = 1.0f / p.keep;
 
@@ -206,6 +211,8 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
   __shared__ float red[8][10][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long npix = (long long)B * H1 * H1;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
   float acc[10];
 #pragma unroll
   for (int k = 0; k < 10; k++) acc[k] = 0.f;
@@ -264,8 +271,7 @@ extern "C" int hvd_conv1_fwd(const float* x, const float* w, const float* bias, 
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
   Conv1Prologue pro{zero_a, zero_a ? n_a : 0, zero_b, zero_b ? n_b : 0, reinterpret_cast<mnist::StepState*>(step_state), advance_step};
-  conv1_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, w, bias, a1, B, pro);
-  return (int)cudaGetLastError();
+  return (int)tc::launch_pdl(conv1_fwd_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, w, bias, a1, B, pro);
 }
 
 extern "C" int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels,
@@ -274,13 +280,11 @@ extern "C" int hvd_head(float* h_pre, const float* b1, const float* w2, const fl
   if (B < 1) return -1;
   HeadParams p{B, training, backward, HEAD_ROWS, keep, h_pre, b1, w2, b2, labels, dh_pre, g_w2, g_b2, g_b1, probs,
                reinterpret_cast<mnist::StepState*>(step_state)};
-  head_kernel<<<(B + HEAD_ROWS - 1) / HEAD_ROWS, 256, 0, (cudaStream_t)stream>>>(p);
-  return (int)cudaGetLastError();
+  return (int)tc::launch_pdl(head_kernel, dim3((B + HEAD_ROWS - 1) / HEAD_ROWS), dim3(256), 0, (cudaStream_t)stream, p);
 }
 
 extern "C" int hvd_conv1_wgrad(const float* x, const float* da1, float* g_w, float* g_b, int B, void* stream) {
-  conv1_wgrad_kernel<<<148 * 4, 256, 0, (cudaStream_t)stream>>>(x, da1, g_w, g_b, B);
-  return (int)cudaGetLastError();
+  return (int)tc::launch_pdl(conv1_wgrad_kernel, dim3(148 * 4), dim3(256), 0, (cudaStream_t)stream, x, da1, g_w, g_b, B);
 }
 
 extern "C" int hvd_colsum64(const float* m, float* out, long long rows, void* stream) {

@@ -82,6 +82,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();                       // everything above overlapped the previous kernel's tail
 
   if (warp == 0) {
     if (tc::elect_one()) {
@@ -196,8 +198,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cu
     attr = true;
   }
   dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN, p.k_split);
-  k<<<grid, 256, Smem<BN>::TOTAL, st>>>(ta, tb, p);
-  return (int)cudaGetLastError();
+  return (int)tc::launch_pdl(k, grid, dim3(256), Smem<BN>::TOTAL, st, ta, tb, p);
 }
 
 }  // namespace
