@@ -13,8 +13,9 @@
 //        the reduction runs over pixels, so BOTH operands are MN-major: A[(tap,ci)][pixel] and
 //        B[co][pixel] are the activation tensors themselves ([pixel][channel] rows).  One haloed a1
 //        tile (10x10 pixels) per patch serves all 9 taps: per kernel row kh the M atoms are the kw
-//        shifts of the same rows (LBO = one row = 128 B, i.e. overlapping atoms).  Four accumulators
-//        in TMEM: kh = 0,1,2 and one fed by 1 KB of ones that yields the bias gradient for free.
+//        shifts of the same rows (LBO = one row = 128 B, i.e. overlapping atoms).  Three accumulators
+//        in TMEM (kh = 0,1,2).  The bias gradient is a plain column sum of dY2 (hvd_colsum64) that
+//        runs on another branch of the step's DAG, off the critical path.
 //        Each CTA reduces a slice of the pixels (split-K over 8x8 patches) and adds its 288x64 result
 //        into the arena with red.add.v4.
 #include "mnist_common.cuh"
@@ -92,6 +93,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   } else if (warp == 1) {
     if (tc::elect_one()) {
       constexpr uint32_t idesc = tc::make_idesc_tf32(128, 32, 0, 0);
+      const uint64_t dW0 = tc::desc_kmajor(tc::smem_u32(sW));
       tc::mbar_wait(wfull, 0);
       int it = 0, ti = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
@@ -102,17 +104,16 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           const int s = it % STAGES;
           tc::mbar_wait(&full[s], (it / STAGES) & 1);
           tc::tc_fence_after();
-          const uint32_t a = tc::smem_u32(sA + s * A_STAGE);
+          const uint64_t da0 = tc::make_smem_desc(tc::smem_u32(sA + s * A_STAGE), 16, SBO_HALO, 2);
+          const uint64_t dw0 = tc::desc_advance(dW0, half * 4096);
 #pragma unroll
           for (int tap = 0; tap < 9; tap++) {
             const int kh = tap / 3, kw = tap % 3;
             // output (y,x) needs dY2[y-kh][x-kw] = halo row (y+2-kh)*10 + (x+2-kw)
-            const uint32_t a_tap = a + ((2 - kh) * 10 + (2 - kw)) * 128;
-            const uint32_t w = tc::smem_u32(sW + (tap * 2 + half) * 4096);
 #pragma unroll
             for (int k = 0; k < 4; k++)
-              tc::mma_tf32(tmem + as * 32, tc::make_smem_desc(a_tap + k * 32, 16, SBO_HALO, 2),
-                           tc::desc_kmajor(w + k * 32), idesc, (half | tap | k) != 0);
+              tc::mma_tf32(tmem + as * 32, tc::desc_advance(da0, ((2 - kh) * 10 + (2 - kw)) * 128 + k * 32),
+                           tc::desc_advance(dw0, tap * 8192 + k * 32), idesc, (half | tap | k) != 0);
           }
           tc::mma_commit(&empty[s]);
         }
@@ -161,9 +162,9 @@ constexpr int DY_SLOT = 8192;               // box {32 co, 8 w, 8 h, 1 n}
 constexpr int STAGE = HALO_BYTES + 2 * DY_SLOT + 1024;   // + slack so the dummy 4th atom stays in bounds
 constexpr int STAGE_TX = HALO_TX + 2 * DY_SLOT;
 constexpr int STAGES = 4;
-constexpr int ONES_BYTES = 1024;            // 8 k-rows of ones, shared by all four M atoms (LBO = 0)
+constexpr int ONES_BYTES = 1024;            // spare 1 KB between the stages and the barriers
 constexpr int SMEM_BYTES = STAGES * STAGE + ONES_BYTES + 1024 + 256;
-constexpr int TMEM_COLS = 256;              // kh = 0,1,2 accumulators + the bias accumulator, 64 columns each
+constexpr int TMEM_COLS = 256;              // kh = 0,1,2 accumulators, 64 columns each (power-of-two allocation)
 
 struct Params {
   int B, n_patches, patches_per_cta;
@@ -193,7 +194,6 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
-  for (int i = threadIdx.x; i < ONES_BYTES / 4; i += blockDim.x) reinterpret_cast<float*>(sOnes)[i] = 1.0f;
   // the slack rows after each halo tile are read by the dummy 4th atom: keep them finite
   for (int i = threadIdx.x; i < STAGES * 128; i += blockDim.x)       // rows 100..103 of each halo slot
     reinterpret_cast<float*>(smem + (i / 128) * STAGE + HALO_TX)[i % 128] = 0.f;
@@ -222,21 +222,20 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   } else if (warp == 1) {
     if (tc::elect_one()) {
       constexpr uint32_t idesc = tc::make_idesc_tf32(128, 64, 1, 1);
-      const uint32_t ones = tc::smem_u32(sOnes);
       for (int i = 0; i < np; i++) {
         const int s = i % STAGES;
         tc::mbar_wait(&full[s], (i / STAGES) & 1);
         tc::tc_fence_after();
         const uint32_t halo = tc::smem_u32(smem + s * STAGE);
         const uint32_t dy = halo + HALO_BYTES;
+        const uint64_t da0 = tc::make_smem_desc(halo, 128, 512, 1);
+        const uint64_t db0 = tc::desc_mnmajor(dy, DY_SLOT);
 #pragma unroll
         for (int ks = 0; ks < 8; ks++) {       // output row ks of the patch = 8 pixels = one K=8 MMA step
-          const uint64_t db = tc::desc_mnmajor(dy + ks * 1024, DY_SLOT);
 #pragma unroll
           for (int kh = 0; kh < 3; kh++)       // M atoms = kw 0,1,2 (+1 dummy): the SAME halo rows shifted by one row each
-            tc::mma_tf32(tmem + kh * 64, tc::make_smem_desc(halo + (ks + kh) * 10 * 128, 128, 512, 1), db, idesc,
-                         (i | ks) != 0);
-          tc::mma_tf32(tmem + 192, tc::make_smem_desc(ones, 0, 512, 1), db, idesc, (i | ks) != 0);   // bias gradient
+            tc::mma_tf32(tmem + kh * 64, tc::desc_advance(da0, (ks + kh) * 10 * 128), tc::desc_advance(db0, ks * 1024),
+                         idesc, (i | ks) != 0);
         }
         tc::mma_commit(&empty[s]);
       }
@@ -247,19 +246,16 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc::mbar_wait(accf, 0);                   // accumulator row: kw = q, ci = lane
     tc::tc_fence_after();
 #pragma unroll 1
-    for (int g = 0; g < 4; g++) {
-      if (g < 3 && q == 3) continue;          // 4th atom of a kh accumulator is the dummy shift
-      if (g == 3 && q != 0) continue;         // bias accumulator: every row is the same column sum (warp-uniform skip)
+    for (int g = 0; g < 3; g++) {
+      if (q == 3) continue;                   // 4th atom of a kh accumulator is the dummy shift
 #pragma unroll 1
       for (int c = 0; c < 64; c += 32) {
         float v[32];
         tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + g * 64 + c, v);
         tc::tmem_ld_wait();
-        float* d = (g < 3) ? p.g_w + ((long long)(g * 3 + q) * 32 + lane) * 64 + c : p.g_b + c;
-        if (g < 3 || lane == 0) {
+        float* d = p.g_w + ((long long)(g * 3 + q) * 32 + lane) * 64 + c;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
-        }
+        for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
       }
     }
   }
@@ -294,7 +290,8 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
   return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(256), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);
 }
 
-// g_w / g_b are ACCUMULATED into (red.add): the caller zeroes them before the step.
+// g_w is ACCUMULATED into (red.add): the caller zeroes it before the step.  g_b is not written here any
+// more (kept in the signature for ABI stability): use hvd_colsum64(dy2, g_b, B*576).
 extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream) {
   CUtensorMap tmA, tmG;
   {

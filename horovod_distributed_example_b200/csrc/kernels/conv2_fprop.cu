@@ -92,6 +92,7 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   } else if (warp == 1) {
     if (tc::elect_one()) {
       constexpr uint32_t idesc = tc::make_idesc_tf32(128, 64, 0, 1);
+      const uint64_t dW0 = tc::desc_mnmajor(tc::smem_u32(sW), 4096);
       tc::mbar_wait(wfull, 0);
       int it = 0, ti = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
@@ -102,14 +103,14 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           const int s = it % STAGES;
           tc::mbar_wait(&full[s], (it / STAGES) & 1);
           tc::tc_fence_after();
-          const uint32_t a = tc::smem_u32(sA + s * A_STAGE);
+          const uint64_t da0 = tc::make_smem_desc(tc::smem_u32(sA + s * A_STAGE), 16, SBO_HALO, 2);
+          const uint64_t dw0 = tc::desc_advance(dW0, kh * 3 * 8192);
 #pragma unroll
           for (int kw = 0; kw < 3; kw++) {
-            const uint32_t w = tc::smem_u32(sW + (kh * 3 + kw) * 8192);
 #pragma unroll
             for (int k = 0; k < 4; k++)     // the tap shift is a row offset into the shared halo tile
-              tc::mma_tf32(tmem + as * 64, tc::make_smem_desc(a + kw * 128 + k * 32, 16, SBO_HALO, 2),
-                           tc::desc_mnmajor(w + k * 1024, 4096), idesc, (kh | kw | k) != 0);
+              tc::mma_tf32(tmem + as * 64, tc::desc_advance(da0, kw * 128 + k * 32),
+                           tc::desc_advance(dw0, kw * 8192 + k * 1024), idesc, (kh | kw | k) != 0);
           }
           tc::mma_commit(&empty[s]);
         }

@@ -255,6 +255,8 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
 __global__ void __launch_bounds__(256) colsum64_kernel(const float* __restrict__ m, float* out, long long rows) {
   __shared__ float red[4][64];
   const int c = threadIdx.x & 63, g = threadIdx.x >> 6;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
   float acc = 0.f;
   for (long long r = (long long)blockIdx.x * 4 + g; r < rows; r += (long long)gridDim.x * 4) acc += m[r * 64 + c];
   red[g][c] = acc;

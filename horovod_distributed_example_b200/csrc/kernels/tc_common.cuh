@@ -144,6 +144,11 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
   d |= (uint64_t)layout << 61;
   return d;
 }
+// Advance a descriptor's start address by `bytes` (a multiple of 16): one 64-bit add instead of
+// rebuilding the descriptor - the single MMA-issuing thread is latency-bound on its own instruction
+// stream, so descriptor arithmetic is kept to a minimum in the hot loops.
+__device__ __forceinline__ uint64_t desc_advance(uint64_t desc, uint32_t bytes) { return desc + (uint64_t)(bytes >> 4); }
+
 // K-major tile, rows of 128 B (32 tf32 along K), 8-row groups 1024 B apart.
 __device__ __forceinline__ uint64_t desc_kmajor(uint32_t smem_addr) { return make_smem_desc(smem_addr, 16, 1024); }
 // MN-major tile built from TMA boxes [KROWS k-rows][32 mn] (128 B rows, ATOM_32B swizzle): MN atoms
