@@ -51,10 +51,9 @@ def main():
     for bn in (64, 128):
         res[f"dense1_dx_unpool_bn{bn}"] = timeit(lambda: tc_gemm(e.dh_pre, P("f1", "kernel"), 128, 9216, 128, False, False, bn, epilogue=EPI_UNPOOL, out=e.dy2.view(-1, 64), mask=e.mask2, scale=1.0 / e.keep1, stream=s))
     res["dense1_dw"] = timeit(lambda: tc_gemm(e.p2, e.dh_pre, 9216, 128, 128, True, True, 128, epilogue=EPI_STORE, out=G("f1", "kernel", 0), stream=s))
-    res["conv2_dgrad"] = timeit(lambda: lib.hvd_conv2_dgrad(e.dy2.data_ptr(), P("c2", "kernel").data_ptr(), e.a1.data_ptr(), e.da1.data_ptr(), 128, 0, s))
+    res["conv2_dgrad"] = timeit(lambda: lib.hvd_conv2_dgrad(e.dy2.data_ptr(), P("c2", "kernel").data_ptr(), e.a1.data_ptr(), None, 128, 0, s, e.x_in.data_ptr(), G("c1", "kernel", 0).data_ptr(), G("c1", "bias", 0).data_ptr()))
     for ctas in (72, 144):
         res[f"conv2_wgrad_ctas{ctas}"] = timeit(lambda: lib.hvd_conv2_wgrad(e.a1.data_ptr(), e.dy2.data_ptr(), G("c2", "kernel", 0).data_ptr(), G("c2", "bias", 0).data_ptr(), 128, ctas, s))
-    res["conv1_wgrad"] = timeit(lambda: lib.hvd_conv1_wgrad(e.x_in.data_ptr(), e.da1.data_ptr(), G("c1", "kernel", 0).data_ptr(), G("c1", "bias", 0).data_ptr(), 128, s))
     if e.fused is not None:
         for i in range(len(e.fused.buckets)):
             res[f"fused_update_bucket{i}"] = timeit(lambda: e.fused.run_bucket(i, 0, 1))

@@ -26,12 +26,13 @@ using namespace mnist;
 
 // ============================================================================ dgrad
 namespace dg {
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;
 constexpr int A_STAGE = 24 * 1024;          // box {32 co, 10 w, 18 h, 1 n} = 180 rows x 128 B (23,040 B)
 constexpr int A_TX = 180 * 128;
 constexpr int W_BYTES = 18 * 4096;
-constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 1024 + 256;
-constexpr int TMEM_COLS = 64;               // 2 stages x 32 columns
+constexpr int STG_BYTES = 32 * 1024;        // fused conv1-wgrad staging: im2col(x) tile 16 KB + da1 tile 16 KB
+constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 2 * STG_BYTES + 1024 /*base align*/ + 1024 /*barriers*/ + 256;
+constexpr int TMEM_COLS = 128;              // 2 dgrad stages x 32 columns + 32 columns for the conv1 wgrad accumulator
 constexpr int TH = 16, TW = 8;              // output tile: 16 rows x 8 columns = 128 pixels
 constexpr int TILES_X = 4;                  // 26 = 3*8 + 2 -> 4 column tiles; 26 = 16 + 10 -> 2 row tiles
 constexpr uint32_t SBO_HALO = 10 * 128;
@@ -39,8 +40,17 @@ constexpr uint32_t SBO_HALO = 10 * 128;
 struct Params {
   int B, n_tiles;
   const float* a1;
-  float* da1;
+  float* da1;                 // optional: written only when non-null (the engine does not need it)
+  const float* x;             // [B,28,28] network input, for the fused conv1 weight gradient (null = off)
+  float* g_w1;                // [9][32]  accumulated with red.add
+  float* g_b1;                // [32]
 };
+
+// Row r of an MN-major staging tile (128 B per row, SWIZZLE_128B_BASE32B): 32-byte chunk c lives at
+// chunk position c ^ (r & 3).
+__device__ __forceinline__ float* stg_chunk(uint8_t* tile, int r, int c) {
+  return reinterpret_cast<float*>(tile + r * 128 + ((c ^ (r & 3)) << 5));
+}
 
 __global__ void __launch_bounds__(256, 1)
 conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmW, Params p) {
@@ -54,14 +64,23 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   uint64_t* wfull = bars + 2 * STAGES;
   uint64_t* accf = wfull + 1;
   uint64_t* acce = accf + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acce + 2);
+  uint64_t* stgf = acce + 2;           // [2] staging tile written by the epilogue
+  uint64_t* stge = stgf + 2;           // [2] staging tile consumed by the tensor core
+  uint64_t* w1done = stge + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w1done + 1);
+  uint8_t* sStg = sA + STAGES * A_STAGE + 1024;  // the barrier block owns the 1 KB in between (keeps 1024 B alignment)
+  const bool fuse_w1 = p.x != nullptr;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) { tc::tma_prefetch_desc(&tmG); tc::tma_prefetch_desc(&tmW); }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
     tc::mbar_init(wfull, 1);
-    for (int s = 0; s < 2; s++) { tc::mbar_init(&accf[s], 1); tc::mbar_init(&acce[s], 128); }
+    for (int s = 0; s < 2; s++) {
+      tc::mbar_init(&accf[s], 1); tc::mbar_init(&acce[s], 128);
+      tc::mbar_init(&stgf[s], 128); tc::mbar_init(&stge[s], 1);
+    }
+    tc::mbar_init(w1done, 1);
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -93,7 +112,23 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   } else if (warp == 1) {
     if (tc::elect_one()) {
       constexpr uint32_t idesc = tc::make_idesc_tf32(128, 32, 0, 0);
+      constexpr uint32_t idesc_w1 = tc::make_idesc_tf32(128, 32, 1, 1);
       const uint64_t dW0 = tc::desc_kmajor(tc::smem_u32(sW));
+      // Fused conv1 weight gradient: dW1[tap][c] (+ db1 as "tap" 9) = sum over the tile's 128 pixels of
+      // im2col(x)[pixel][tap] * da1[pixel][c].  Both staging tiles are [pixel][32] rows written by the
+      // epilogue = MN-major operands with K = pixels: 16 MMAs (K=8) per tile into TMEM columns 64..95.
+      auto w1_mma = [&](int tj) {
+        const int sb = tj & 1;
+        tc::mbar_wait(&stgf[sb], (tj >> 1) & 1);
+        tc::tc_fence_after();
+        const uint32_t st = tc::smem_u32(sStg + sb * STG_BYTES);
+        const uint64_t dA = tc::make_smem_desc(st, 0, 512, 1);            // LBO 0: the four M atoms coincide
+        const uint64_t dB = tc::make_smem_desc(st + 16384, 0, 512, 1);
+#pragma unroll
+        for (int ks = 0; ks < 16; ks++)
+          tc::mma_tf32(tmem + 64, tc::desc_advance(dA, ks * 1024), tc::desc_advance(dB, ks * 1024), idesc_w1, (tj | ks) != 0);
+        tc::mma_commit(&stge[sb]);
+      };
       tc::mbar_wait(wfull, 0);
       int it = 0, ti = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
@@ -118,6 +153,11 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           tc::mma_commit(&empty[s]);
         }
         tc::mma_commit(&accf[as]);
+        if (fuse_w1 && ti > 0) w1_mma(ti - 1);          // conv1 wgrad of the PREVIOUS tile (its epilogue ran meanwhile)
+      }
+      if (fuse_w1) {
+        if (ti > 0) w1_mma(ti - 1);
+        tc::mma_commit(w1done);
       }
     }
   } else if (warp >= 4) {
@@ -135,16 +175,71 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       tc::mbar_arrive(&acce[as]);
       const int b = tile / 8, ty = (tile % 8) / TILES_X, tx = tile % TILES_X;
       const int y = ty * TH + (r >> 3), x = tx * TW + (r & 7);
-      if (y < H1 && x < H1) {
-        const long long off = (((long long)b * H1 + y) * H1 + x) * C1;
+      const bool valid = y < H1 && x < H1;
+      const long long off = (((long long)b * H1 + y) * H1 + x) * C1;
+      if (valid) {
         const float4* act = reinterpret_cast<const float4*>(p.a1 + off);
-        float4* dst = reinterpret_cast<float4*>(p.da1 + off);
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
+        for (int j = 0; j < 8; j++) {                    // conv1's ReLU backward
           const float4 a = __ldg(act + j);
-          dst[j] = make_float4(a.x > 0.f ? v[4 * j] : 0.f, a.y > 0.f ? v[4 * j + 1] : 0.f,
-                               a.z > 0.f ? v[4 * j + 2] : 0.f, a.w > 0.f ? v[4 * j + 3] : 0.f);
+          v[4 * j] = a.x > 0.f ? v[4 * j] : 0.f;         v[4 * j + 1] = a.y > 0.f ? v[4 * j + 1] : 0.f;
+          v[4 * j + 2] = a.z > 0.f ? v[4 * j + 2] : 0.f; v[4 * j + 3] = a.w > 0.f ? v[4 * j + 3] : 0.f;
         }
+        if (p.da1) {
+          float4* dst = reinterpret_cast<float4*>(p.da1 + off);
+#pragma unroll
+          for (int j = 0; j < 8; j++) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+      }
+      if (fuse_w1) {
+        const int sb = ti & 1;
+        tc::mbar_wait(&stge[sb], ((ti >> 1) & 1) ^ 1);    // the tensor core is done with this staging tile
+        uint8_t* tA = sStg + sb * STG_BYTES;
+        uint8_t* tB = tA + 16384;
+        float xin[12];
+#pragma unroll
+        for (int k = 0; k < 12; k++) xin[k] = 0.f;
+        if (valid) {
+          const float* xi = p.x + ((long long)b * IMG + y) * IMG + x;
+#pragma unroll
+          for (int kh = 0; kh < 3; kh++)
+#pragma unroll
+            for (int kw = 0; kw < 3; kw++) xin[kh * 3 + kw] = __ldg(xi + kh * IMG + kw);
+          xin[9] = 1.0f;                                  // the bias "tap"
+        }
+        float4* a0 = reinterpret_cast<float4*>(stg_chunk(tA, r, 0));
+        a0[0] = make_float4(xin[0], xin[1], xin[2], xin[3]);
+        a0[1] = make_float4(xin[4], xin[5], xin[6], xin[7]);
+        float4* a1c = reinterpret_cast<float4*>(stg_chunk(tA, r, 1));
+        a1c[0] = make_float4(xin[8], xin[9], 0.f, 0.f);
+        a1c[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int c = 2; c < 4; c++) {
+          float4* z = reinterpret_cast<float4*>(stg_chunk(tA, r, c));
+          z[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+          z[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+          float4* d = reinterpret_cast<float4*>(stg_chunk(tB, r, c));
+          d[0] = valid ? make_float4(v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+          d[1] = valid ? make_float4(v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        tc::fence_proxy_async();                          // generic-proxy smem writes -> visible to the tensor core
+        tc::mbar_arrive(&stgf[sb]);
+      }
+    }
+    if (fuse_w1 && q == 0) {
+      // rows 0..8 of the conv1-wgrad accumulator are the 9 taps, row 9 is the bias gradient
+      tc::mbar_wait(w1done, 0);
+      tc::tc_fence_after();
+      float w[32];
+      tc::tmem_ld_x32(tmem + 64, w);
+      tc::tmem_ld_wait();
+      if (ti > 0 && lane < 10) {
+        float* d = lane < 9 ? p.g_w1 + lane * 32 : p.g_b1;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, w[j], w[j + 1], w[j + 2], w[j + 3]);
       }
     }
   }
@@ -267,7 +362,10 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
 }  // namespace
 
-extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a1, float* da1, int B, int ctas, void* stream) {
+// da1 may be NULL.  When x is non-NULL the conv1 weight/bias gradients are accumulated (red.add) into
+// g_w1 [9][32] / g_b1 [32] inside the same kernel (no separate conv1-wgrad pass, no da1 round trip).
+extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a1, float* da1, int B, int ctas,
+                               void* stream, const float* x, float* g_w1, float* g_b1) {
   CUtensorMap tmG, tmW;
   {
     uint64_t dims[4] = {64, 24, 24, (uint64_t)B};
@@ -284,7 +382,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
     if (cudaFuncSetAttribute(dg::conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dg::SMEM_BYTES) != cudaSuccess) return -10;
     attr = true;
   }
-  dg::Params p{B, B * 8, a1, da1};
+  dg::Params p{B, B * 8, a1, da1, x, g_w1, g_b1};
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
   return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(256), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);

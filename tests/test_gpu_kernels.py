@@ -188,7 +188,11 @@ def test_conv2_dgrad_and_wgrad_and_conv1_wgrad():
     da_ref = (a_in.grad.permute(0, 2, 3, 1) * (a1r > 0)).float()
     dw_ref = wt.grad.permute(2, 3, 1, 0).float()                  # OIHW -> HWIO
     da1 = torch.full_like(a1, 5.0)
-    assert lib.hvd_conv2_dgrad(dy2.data_ptr(), w2.data_ptr(), a1r.data_ptr(), da1.data_ptr(), B, 0, _s()) == 0
+    f1w = torch.zeros(3, 3, 1, 32, device="cuda")
+    f1b = torch.zeros(32, device="cuda")
+    lib.hvd_conv2_dgrad.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 4
+    assert lib.hvd_conv2_dgrad(dy2.data_ptr(), w2.data_ptr(), a1r.data_ptr(), da1.data_ptr(), B, 0, _s(),
+                               x.data_ptr(), f1w.data_ptr(), f1b.data_ptr()) == 0
     assert _rel(da1, da_ref) < 3e-3
     gw = torch.zeros(3, 3, 32, 64, device="cuda")
     gb = torch.zeros(64, device="cuda")
@@ -206,6 +210,9 @@ def test_conv2_dgrad_and_wgrad_and_conv1_wgrad():
     F.conv2d(xin, w1).backward(da_ref.permute(0, 3, 1, 2).double())
     assert _rel(g1w, w1.grad.permute(2, 3, 1, 0)) < 1e-4
     assert _rel(g1b, da_ref.double().sum(dim=(0, 1, 2))) < 1e-4
+    # the same gradients from the tensor-core GEMM fused into the dgrad kernel (TF32 operands)
+    assert _rel(f1w, w1.grad.permute(2, 3, 1, 0)) < 3e-3
+    assert _rel(f1b, da_ref.double().sum(dim=(0, 1, 2))) < 3e-3
 
 
 def _models(rate1, rate2, opt_name):
