@@ -64,10 +64,18 @@ __device__ __forceinline__ float4 update_f4(float4 g, float4 p, float4& s0, floa
   return p;
 }
 
-constexpr int kUnroll = 2;
+// NR = compile-time bound on the rank count (1, 2, 4, 8).  Fewer peers leave registers for a deeper
+// unroll: the kernel is a latency-bound stream, so every thread keeps as many 16-byte loads in flight
+// as its register budget allows (NVLS needs one load per element whatever the rank count).
+template <int VARIANT, int NR>
+struct Unroll { static constexpr int value = (VARIANT == HVD_NVLS || NR <= 2) ? 4 : 2; };
 
-template <int VARIANT, int KIND>
-__global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedArgs a) {
+// <= 128 registers per thread (two CTAs per SM) on purpose: in the training step this kernel overlaps
+// the conv backward kernels, whose CTAs pin every SM's shared memory; it only gets on an SM if its
+// register footprint fits beside them.
+template <int VARIANT, int KIND, int NR>
+__global__ void __launch_bounds__(256, 2) hvd_fused_kernel(HvdCommCtx c, HvdFusedArgs a) {
+  constexpr int kUnroll = Unroll<VARIANT, NR>::value;
   const int rank = hvd_rank(c);
   const int N = c.nranks;
   const uint32_t ep = hvd_epoch_load(c, a.slot);
@@ -115,12 +123,12 @@ __global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedAr
         if (idx < i1) acc[u] = multimem_ld_reduce_f4(c.mc_base + a.grad_off + s + idx * 4);
       }
     } else {
-      float4 v[kUnroll][HVD_MAX_RANKS];
+      float4 v[kUnroll][NR];
 #pragma unroll
       for (int u = 0; u < kUnroll; u++) {
         const long long idx = i + (long long)u * blockDim.x;
 #pragma unroll
-        for (int r = 0; r < HVD_MAX_RANKS; r++)
+        for (int r = 0; r < NR; r++)
           if (r < N && idx < i1)          // own gradients: plain load (written by earlier kernels on this GPU)
             v[u][r] = (r == rank) ? ld_f4(c.base[r] + a.grad_off + s + idx * 4)
                                   : ld_sys_f4(c.base[r] + a.grad_off + s + idx * 4);
@@ -129,7 +137,7 @@ __global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedAr
       for (int u = 0; u < kUnroll; u++) {
         acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int r = 0; r < HVD_MAX_RANKS; r++)      // fixed order: identical bits on every rank
+        for (int r = 0; r < NR; r++)                 // fixed order: identical bits on every rank
           if (r < N) { acc[u].x += v[u][r].x; acc[u].y += v[u][r].y; acc[u].z += v[u][r].z; acc[u].w += v[u][r].w; }
       }
     }
@@ -153,7 +161,7 @@ __global__ void __launch_bounds__(256) hvd_fused_kernel(HvdCommCtx c, HvdFusedAr
         *reinterpret_cast<float4*>(mine + dst_off) = res;
       } else if (VARIANT == HVD_TWOSHOT) {
 #pragma unroll
-        for (int r = 0; r < HVD_MAX_RANKS; r++)
+        for (int r = 0; r < NR; r++)
           if (r < N) {
             if (r == rank) *reinterpret_cast<float4*>(mine + dst_off) = res;
             else st_sys_f4(c.base[r] + dst_off, res);
@@ -191,14 +199,22 @@ __global__ void __launch_bounds__(512) hvd_bcast_kernel(HvdCommCtx c, int slot, 
 }
 
 // ------------------------------------------------------------------------------ launchers
-template <int V, int K>
-static cudaError_t launch_vk(const HvdCommCtx& c, const HvdFusedArgs& a, int ctas, int threads, cudaStream_t st, int emu) {
+template <int V, int K, int NR>
+static cudaError_t launch_vkn(const HvdCommCtx& c, const HvdFusedArgs& a, int ctas, int threads, cudaStream_t st, int emu) {
   if (emu > 0) {
     void* args[] = {(void*)&c, (void*)&a};
-    return cudaLaunchCooperativeKernel((void*)hvd_fused_kernel<V, K>, dim3(ctas, emu), dim3(threads), args, 0, st);
+    return cudaLaunchCooperativeKernel((void*)hvd_fused_kernel<V, K, NR>, dim3(ctas, emu), dim3(threads), args, 0, st);
   }
-  hvd_fused_kernel<V, K><<<ctas, threads, 0, st>>>(c, a);
+  hvd_fused_kernel<V, K, NR><<<ctas, threads, 0, st>>>(c, a);
   return cudaGetLastError();
+}
+
+template <int V, int K>
+static cudaError_t launch_vk(const HvdCommCtx& c, const HvdFusedArgs& a, int ctas, int threads, cudaStream_t st, int emu) {
+  if (c.nranks <= 1) return launch_vkn<V, K, 1>(c, a, ctas, threads, st, emu);
+  if (c.nranks <= 2) return launch_vkn<V, K, 2>(c, a, ctas, threads, st, emu);
+  if (c.nranks <= 4) return launch_vkn<V, K, 4>(c, a, ctas, threads, st, emu);
+  return launch_vkn<V, K, 8>(c, a, ctas, threads, st, emu);
 }
 
 template <int V>

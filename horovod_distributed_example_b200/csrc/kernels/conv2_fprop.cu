@@ -29,7 +29,8 @@ constexpr int A_STAGE = 20 * 1024;          // one kh: box {32 c, 10 w, 8 h, 2 n
 constexpr int W_BYTES = 9 * 8192;           // 9 taps x [32 cin][64 cout] fp32
 constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 1024 + 256;
 constexpr int TMEM_COLS = 128;              // 2 accumulator stages x 64 columns
-constexpr int EPI_WARPS = 8;                // 2 per TMEM lane quadrant (one per 32-column chunk)
+constexpr int EPI_SETS = 2;                 // warp sets: set s drains accumulator stage s (tiles alternate)
+constexpr int EPI_WARPS = 8 * EPI_SETS;     // per set: 2 warps per TMEM lane quadrant (one per 32-column chunk)
 constexpr int THREADS = 128 + EPI_WARPS * 32;
 constexpr uint32_t SBO_HALO = 10 * 128;     // next output row = 10 halo rows further
 
@@ -61,7 +62,7 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
     tc::mbar_init(wfull, 1);
-    for (int s = 0; s < 2; s++) { tc::mbar_init(&accf[s], 1); tc::mbar_init(&acce[s], EPI_WARPS * 32); }
+    for (int s = 0; s < 2; s++) { tc::mbar_init(&accf[s], 1); tc::mbar_init(&acce[s], 8 * 32); }
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -119,7 +120,8 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     }
   } else if (warp >= 4) {
     const int q = warp & 3;                      // TMEM lane quadrant
-    const int c = (warp - 4) >> 2;               // which 32-channel chunk this warp handles
+    const int c = ((warp - 4) >> 2) & 1;         // which 32-channel chunk this warp handles
+    const int wset = (warp - 4) >> 3;            // warp set 0 drains even tiles (stage 0), set 1 odd tiles
     const int r = q * 32 + lane;                 // accumulator row = pixel inside the tile
     const int half = r >> 6, hl = (r & 63) >> 3, wl = r & 7;
     const int wp = (lane & 1) | ((lane >> 2) & 2);   // position inside the 2x2 window (dy*2+dx)
@@ -132,6 +134,7 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     int ti = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
       const int as = ti & 1;
+      if (EPI_SETS == 2 && as != wset) continue;
       tc::mbar_wait(&accf[as], (ti >> 1) & 1);
       tc::tc_fence_after();
       float v[32];

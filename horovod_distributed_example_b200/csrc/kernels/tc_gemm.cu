@@ -8,11 +8,12 @@
 // B K-major) and wgrad (X^T * dY: A MN-major, B MN-major) of the reference's Dense(128) layer
 // (mnist_keras.py:79) are all this kernel.
 //
-// Structure (one CTA per output tile or per split-K slice, 256 threads):
+// Structure (one CTA per output tile or per split-K slice, 384 threads):
 //   warp 0 : TMA producer          (one elected lane; 4-stage smem ring, mbarrier full/empty)
 //   warp 1 : MMA issuer            (one elected lane; tcgen05.mma kind::tf32, accumulator in TMEM)
 //   warp 2 : TMEM allocator
-//   warps 4-7 : epilogue           (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+//   warps 4-11: epilogue           (tcgen05.ld 32x32b -> registers -> fused epilogue -> global; two warps
+//                                   per TMEM lane quadrant, each taking every other 32-column chunk)
 #include "tc_common.cuh"
 
 namespace {
@@ -48,7 +49,7 @@ struct Smem {
 };
 
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(384, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -131,7 +132,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc::tc_fence_after();
     const int row = m0 + q * 32 + lane;
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = ((warp - 4) >> 2) * 32; c < BN; c += 64) {     // two warps per lane quadrant split the column chunks
       float v[32];
       tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + c, v);
       tc::tmem_ld_wait();
@@ -198,7 +199,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cu
     attr = true;
   }
   dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN, p.k_split);
-  return (int)tc::launch_pdl(k, grid, dim3(256), Smem<BN>::TOTAL, st, ta, tb, p);
+  return (int)tc::launch_pdl(k, grid, dim3(384), Smem<BN>::TOTAL, st, ta, tb, p);
 }
 
 }  // namespace
