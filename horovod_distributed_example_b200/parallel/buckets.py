@@ -11,7 +11,7 @@ the next tensor would exceed ``HVD_FUSION_THRESHOLD`` bytes, or at explicit cut 
 (the MNIST engine cuts after ``dense_1/kernel`` so 98% of the bytes start reducing while
 the conv backward is still running).
 
-The planner itself is native (``csrc/core/bucket_plan.cpp`` via ``libhvd_core.so``); the
+The planner itself is native (``csrc/core/core.cpp: hvd_plan_buckets`` via ``libhvd_core.so``); the
 pure-Python twin below is the oracle for its unit test and the fallback when the
 library has not been built.
 """
@@ -72,9 +72,10 @@ def plan_python(offsets: Sequence[int], numels: Sequence[int], slab_elems: int,
 
 
 def plan_hash(names: Sequence[str], shapes: Sequence[Sequence[int]], buckets: Sequence[Bucket]) -> int:
+    # Shapes and order only: layer names are auto-numbered per process (a rank that built another
+    # model first - e.g. rank 0 reloading a checkpoint - would otherwise disagree for no reason).
     h = 0xCBF29CE484222325
-    for nme, shp in zip(names, shapes):
-        h = _fnv1a(h, nme.encode())
+    for _nme, shp in zip(names, shapes):
         h = _fnv1a(h, (",".join(str(int(s)) for s in shp) + ";").encode())
     for b in buckets:
         h = _fnv1a(h, f"{b.start}:{b.end}|".encode())

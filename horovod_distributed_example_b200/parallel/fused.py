@@ -36,10 +36,48 @@ class FusedReducer:
             v, c = vt.pick(b.nbytes, self.ctx.size, bool(buf.mc_ptr), forced, cfg.comm_ctas if cfg else 0)
             if variants is not None:
                 v = variants[i]
+            elif cfg is not None and cfg.autotune and forced == "auto" and self.ctx.size > 1 and not self.ctx.emulated:
+                v, c = self._autotune(b.nbytes, bool(buf.mc_ptr))
             self.variants.append(v)
             self.ctas.append(c)
         self.side_stream = torch.cuda.Stream(device=arena.device)
         self._events = [torch.cuda.Event() for _ in self.buckets]
+
+    def _autotune(self, nbytes: int, has_nvls: bool):
+        """HVD_AUTOTUNE=1: measure every variant x a few CTA counts for this bucket's size on the staging
+        buffer (device-timed, max over ranks) and keep the fastest - the measured-latency replacement
+        of Horovod's Bayesian autotuner.  Collective: every rank runs the same candidates in order."""
+        from .. import collectives
+        ctx = self.ctx
+        cap = ctx.staging_bytes // 8
+        n = min(nbytes // 4, cap) // 4 * 4
+        best = None
+        log = []
+        for v in (ONESHOT, TWOSHOT) + ((NVLS,) if has_nvls and ctx.staging.mc_ptr else ()):
+            for ctas in sorted({1, 8, 32, 148}):
+                a = HvdFusedArgs()
+                a.start, a.end, a.grad_off = 0, n, 0
+                a.out_off = cap if v == ONESHOT else 0
+                a.scale, a.kind, a.variant, a.slot, a.exit_barrier = 1.0, 0, v, peer_mod.SLOT_STAGING, 1
+                for _ in range(2):
+                    ctx.launch_fused(ctx.staging, a, ctas)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(5):
+                    ctx.launch_fused(ctx.staging, a, ctas)
+                e1.record()
+                torch.cuda.synchronize()
+                t = max(collectives.allgather_object(e0.elapsed_time(e1) / 5))
+                log.append({"bytes": n * 4, "variant": VARIANT_NAMES[v], "ctas": ctas, "ms": t})
+                if best is None or t < best[0]:
+                    best = (t, v, ctas)
+        cfg = basics.state().config
+        if cfg.autotune_log and ctx.rank == 0:
+            import json
+            with open(cfg.autotune_log, "a") as f:
+                for r in log:
+                    f.write(json.dumps(r) + "\n")
+        return best[1], best[2]
 
     def describe(self) -> List[str]:
         return [f"bucket{b.index}[{b.start}:{b.end}] {b.nbytes}B {VARIANT_NAMES[v]} ctas={c}"

@@ -113,6 +113,45 @@ def tf2_script_flow():
     print("OK")
 
 
+def resume_from_checkpoint():
+    """Resume path: rank 0 restores a checkpoint, the broadcast callback makes
+    every rank identical to it (weights, optimizer slots, iteration counter), training continues."""
+    hvd.init()
+    r = hvd.rank()
+    path = os.path.join(os.environ["HVD_TEST_OUT"], "ckpt.h5")
+    rng = np.random.default_rng(5)
+    x = rng.random((64, 28, 28, 1), dtype=np.float32)
+    y = rng.integers(0, 10, 64)
+    if r == 0:
+        m0 = _mnist_model(seed=1)
+        m0.compile(loss=keras.losses.SparseCategoricalCrossentropy(), optimizer=keras.optimizers.Adam(0.01))
+        for _ in range(3):
+            m0.train_on_batch(x, y)
+        m0.save(path)
+    hvd.barrier()
+    m = _mnist_model(seed=50 + r)
+    opt = hvd.DistributedOptimizer(keras.optimizers.Adam(0.01))
+    m.compile(loss=keras.losses.SparseCategoricalCrossentropy(), optimizer=opt, metrics=['accuracy'])
+    m._ensure_built(x.shape)
+    if r == 0:
+        restored = keras.load_model(path)                 # rank-0-only load, as in the reference
+        m.set_weights(restored.get_weights())
+        for a, b in zip(m.arena.slots, restored.arena.slots):
+            a.copy_(b)
+        opt.iterations = restored.optimizer.iterations
+    cb = hvd.callbacks.BroadcastGlobalVariablesCallback(0)
+    cb.set_model(m)
+    cb.on_train_begin()
+    st = hvd.allgather(torch.cat([m.arena.params, m.arena.slots[0], m.arena.slots[1]])[None])
+    assert torch.equal(st[0], st[1])
+    assert opt.iterations == 3
+    m.train_on_batch(x, y)
+    assert opt.iterations == 4
+    w = hvd.allgather(m.arena.params.clone()[None])
+    assert torch.equal(w[0], w[1])
+    print("OK")
+
+
 def plan_mismatch():
     hvd.init()
     layers = [keras.layers.Flatten(), keras.layers.Dense(4 + hvd.rank())]

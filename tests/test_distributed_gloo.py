@@ -28,3 +28,7 @@ def test_tf2_script_flow_ws2(tmp_path):
 
 def test_bucket_plan_mismatch_detected():
     _ok(run_workers("plan_mismatch"))
+
+
+def test_resume_from_rank0_checkpoint_ws2(tmp_path):
+    _ok(run_workers("resume_from_checkpoint", env={"HVD_TEST_OUT": str(tmp_path)}))
