@@ -38,6 +38,7 @@ class BroadcastGlobalVariablesCallback(Callback):
             return
         if basics.size() > 1:
             m = self.model
+            m._sync_backend()
             arena = m.arena
             with torch.no_grad():
                 collectives.broadcast_(arena.params, self.root_rank, name="broadcast.params")
@@ -127,12 +128,12 @@ class LearningRateScheduleCallback(Callback):
         if hasattr(opt, "momentum") and self.momentum_correction and old_lr > 0:
             self.restore_momentum = opt.momentum
             opt.momentum = opt.momentum * new_lr / old_lr
-            opt._push_hyper()
+            opt._hyper_changed()
 
     def _restore_momentum_if_needed(self):
         if self.restore_momentum is not None:
             self.model.optimizer.momentum = self.restore_momentum
-            self.model.optimizer._push_hyper()
+            self.model.optimizer._hyper_changed()
             self.restore_momentum = None
 
     def on_train_begin(self, logs=None):

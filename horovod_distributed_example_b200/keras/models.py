@@ -134,7 +134,8 @@ class Model:
             from .. import basics
             from ..parallel import peer
             allocator = peer.context().alloc_tensor
-            double = basics.size() > 1       # double-buffered grads drop the one-shot exit barrier
+            double = True                    # double-buffered grads: no one-shot exit barrier, and the big
+                                             # bucket's update may overlap the next step's forward
         self.arena = ar.resize_slots(max(n_slots, ar.n_slots), allocator, double_grads=double)
         self._rebind_weights()
 
@@ -187,7 +188,14 @@ class Model:
             self._finish_compile()
 
     # ---- weights ------------------------------------------------------------------
+    def _sync_backend(self):
+        """Wait for any parameter update the backend still has in flight on a side stream."""
+        be = self._backend
+        if be is not None and hasattr(be, "sync_params"):
+            be.sync_params()
+
     def get_weights(self) -> List[np.ndarray]:
+        self._sync_backend()
         out = []
         for lname, wnames in self._layer_weight_names():
             for w in wnames:
@@ -195,6 +203,7 @@ class Model:
         return out
 
     def set_weights(self, weights: Sequence[np.ndarray]):
+        self._sync_backend()
         it = iter(weights)
         with torch.no_grad():
             for lname, wnames in self._layer_weight_names():
@@ -398,14 +407,17 @@ class Model:
         from ..utils import keras_h5
         if os.path.exists(filepath) and not overwrite:
             raise FileExistsError(filepath)
+        self._sync_backend()
         keras_h5.save_model(self, filepath, include_optimizer=include_optimizer)
 
     def save_weights(self, filepath, overwrite=True):
         from ..utils import keras_h5
+        self._sync_backend()
         keras_h5.save_model(self, filepath, include_optimizer=False, weights_only=True)
 
     def load_weights(self, filepath):
         from ..utils import keras_h5
+        self._sync_backend()
         keras_h5.load_weights_into(self, filepath)
 
     def summary(self, print_fn=print):

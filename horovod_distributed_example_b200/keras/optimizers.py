@@ -46,8 +46,10 @@ class Optimizer:
         self.decay = float(decay)
         self.iterations = 0
         self.name = name or type(self).__name__
-        self._hyper = None      # device fp32[8], created by bind()
+        self._hyper = None      # device fp32[2][8], created by bind()
         self._arena = None
+        self._defer_push = False
+        self._hyper_dirty = 0
 
     # -- learning rate is settable at run time (the warmup callback mutates it) --
     @property
@@ -57,7 +59,16 @@ class Optimizer:
     @lr.setter
     def lr(self, v: float):
         self._lr = float(v)
-        self._push_hyper()
+        self._hyper_changed()
+
+    def _hyper_changed(self) -> None:
+        """A hyper-parameter was changed from the host.  Normally both device rows are rewritten now;
+        the fused engine (which may still have the previous step's update kernel in flight) asks for
+        the push to be deferred to the start of the next two steps, one row each."""
+        if getattr(self, "_defer_push", False):
+            self._hyper_dirty = 2
+        else:
+            self._push_hyper(both=True)
 
     learning_rate = lr
 
@@ -75,8 +86,14 @@ class Optimizer:
     # -- binding to an arena ------------------------------------------------------
     def bind(self, arena) -> None:
         self._arena = arena
-        self._hyper = torch.zeros(8, dtype=torch.float32, device=arena.device)
-        self._push_hyper()
+        # two rows: the fused engine alternates rows with its gradient-buffer parity, so the update
+        # kernel of step t (possibly still running on a side stream) never sees step t+1's values
+        self._hyper = torch.zeros(2, 8, dtype=torch.float32, device=arena.device)
+        self._next_slot = 0
+        self._pin_ring = [torch.zeros(8, dtype=torch.float32).pin_memory() for _ in range(8)] \
+            if arena.device.type == "cuda" else None
+        self._pin_i = 0
+        self._push_hyper(both=True)
 
     def _effective_lr(self) -> float:
         lr = self._lr
@@ -93,19 +110,30 @@ class Optimizer:
     def _hyper_values(self) -> List[float]:
         return [self._effective_lr(), 0.0, 0.0, 0.0, float(self.iterations), self.decay, 0.0, 0.0]
 
-    def _push_hyper(self) -> None:
+    def _push_hyper(self, both: bool = False) -> None:
+        """Write the hyper-parameters the NEXT step will use into its row of the device vector."""
         if self._hyper is None:
             return
         vals = torch.tensor(self._hyper_values(), dtype=torch.float32)
+        rows = (0, 1) if both else (self._next_slot,)
         if self._hyper.is_cuda:
-            # tiny async H2D; ordered on the current stream ahead of the next step
-            self._hyper.copy_(vals.pin_memory(), non_blocking=True)
+            # tiny async H2D from a ring of pinned buffers; ordered on the current stream
+            buf = self._pin_ring[self._pin_i % len(self._pin_ring)]
+            self._pin_i += 1
+            buf.copy_(vals)
+            for r in rows:
+                self._hyper[r].copy_(buf, non_blocking=True)
         else:
-            self._hyper.copy_(vals)
+            for r in rows:
+                self._hyper[r].copy_(vals)
 
     @property
     def hyper(self) -> torch.Tensor:
-        return self._hyper
+        """Row 0 of the device hyper-parameter block (fp32[8]); row 1 is the engine's alternate."""
+        return self._hyper[0]
+
+    def hyper_row(self, which: int) -> torch.Tensor:
+        return self._hyper[which & 1]
 
     # -- the update -----------------------------------------------------------------
     def apply_flat(self, params: torch.Tensor, grads: torch.Tensor, slots) -> None:

@@ -158,6 +158,7 @@ class _DistributedMixin:
 
 
 def _check_replicas_impl(arena):
+    torch.cuda.synchronize(arena.device) if arena.device.type == "cuda" else None
     cs = int(arena.checksum())
     all_cs = collectives.allgather_object(cs)
     if any(c != all_cs[0] for c in all_cs):

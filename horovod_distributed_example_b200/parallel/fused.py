@@ -83,7 +83,7 @@ class FusedReducer:
         return [f"bucket{b.index}[{b.start}:{b.end}] {b.nbytes}B {VARIANT_NAMES[v]} ctas={c}"
                 for b, v, c in zip(self.buckets, self.variants, self.ctas)]
 
-    def _args(self, i: int, grad_buf: int, exit_barrier: int) -> HvdFusedArgs:
+    def _args(self, i: int, grad_buf: int, exit_barrier: int, hyper_row=None) -> HvdFusedArgs:
         b, ar = self.buckets[i], self.arena
         a = HvdFusedArgs()
         a.start, a.end = b.start, b.end
@@ -92,13 +92,13 @@ class FusedReducer:
         a.slot0_off = self.base_off + (ar.slot_offset(0) if ar.n_slots > 0 else 0)
         a.slot1_off = self.base_off + (ar.slot_offset(1) if ar.n_slots > 1 else 0)
         a.out_off = a.grad_off
-        a.hyper = self.opt.hyper.data_ptr()
+        a.hyper = self.opt.hyper_row(hyper_row if hyper_row is not None else 0).data_ptr()
         a.scale = 1.0 / self.ctx.size
         a.kind, a.variant, a.slot, a.exit_barrier = self.opt.kind, self.variants[i], i, exit_barrier
         return a
 
-    def run_bucket(self, i: int, grad_buf: int = 0, exit_barrier: int = 1, stream=None) -> None:
-        self.ctx.launch_fused(self.buf, self._args(i, grad_buf, exit_barrier), self.ctas[i], stream=stream)
+    def run_bucket(self, i: int, grad_buf: int = 0, exit_barrier: int = 1, stream=None, hyper_row=None) -> None:
+        self.ctx.launch_fused(self.buf, self._args(i, grad_buf, exit_barrier, hyper_row), self.ctas[i], stream=stream)
 
     def run_all(self, grad_buf: int = 0, exit_barrier: int = 1, stream=None) -> None:
         tl = basics.state().timeline
