@@ -28,7 +28,7 @@ def run_ours(a):
     torch.manual_seed(0)
     net = resnet50().to(memory_format=torch.channels_last)
     m = keras.TorchModel(net, channels_last_input=True)
-    opt = hvd.DistributedOptimizer(keras.optimizers.SGD(0.0125 * n, momentum=0.9))
+    opt = hvd.DistributedOptimizer(keras.optimizers.SGD(0.0125, momentum=0.9)      # fixed LR: random labels diverge at 0.0125*n without warmup)
     m.compile(optimizer=opt, loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True))
     x = torch.randn(a.batch, 224, 224, 3, device="cuda")
     y = torch.randint(0, 1000, (a.batch,), device="cuda")
@@ -70,7 +70,7 @@ def run_ddp(a):
     torch.manual_seed(0)
     net = resnet50().cuda().to(memory_format=torch.channels_last)
     model = torch.nn.parallel.DistributedDataParallel(net, device_ids=[lr], bucket_cap_mb=16, gradient_as_bucket_view=True) if n > 1 else net
-    opt = torch.optim.SGD(net.parameters(), lr=0.0125 * n, momentum=0.9)
+    opt = torch.optim.SGD(net.parameters(), lr=0.0125, momentum=0.9)
     x = torch.randn(a.batch, 3, 224, 224, device="cuda").to(memory_format=torch.channels_last)
     y = torch.randint(0, 1000, (a.batch,), device="cuda")
 

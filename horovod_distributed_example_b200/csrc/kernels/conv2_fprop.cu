@@ -15,7 +15,7 @@
 //   per tap it is [32 cin][64 cout] with cout contiguous = an MN-major operand (2 atoms of 32).
 //
 // Persistent, warp-specialised: warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator,
-// warps 4-7 epilogue.  Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of
+// 16 epilogue warps in two sets.  Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of
 // tile i+1.  The epilogue writes only the pooled, dropped-out activations (4.7 MB instead of the
 // 18.9 MB conv output) plus one mask byte per element (arg-max + keep) for backward.
 #include "mnist_common.cuh"

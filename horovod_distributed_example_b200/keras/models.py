@@ -196,20 +196,15 @@ class Model:
 
     def get_weights(self) -> List[np.ndarray]:
         self._sync_backend()
-        out = []
-        for lname, wnames in self._layer_weight_names():
-            for w in wnames:
-                out.append(self.arena.param(f"{lname}/{w}").detach().cpu().numpy().copy())
-        return out
+        return [self.arena.param(n).detach().cpu().numpy().copy() for n in self.trainable_weight_names()]
 
     def set_weights(self, weights: Sequence[np.ndarray]):
         self._sync_backend()
         it = iter(weights)
         with torch.no_grad():
-            for lname, wnames in self._layer_weight_names():
-                for w in wnames:
-                    p = self.arena.param(f"{lname}/{w}")
-                    p.copy_(torch.as_tensor(next(it)).view_as(p))
+            for n in self.trainable_weight_names():
+                p = self.arena.param(n)
+                p.copy_(torch.as_tensor(next(it)).view_as(p))
         if self._backend is not None and hasattr(self._backend, "weights_changed"):
             self._backend.weights_changed()
 

@@ -84,5 +84,48 @@ def train_replicas():
     print("OK", flush=True)
 
 
+def torchmodel_overlap():
+    """TorchModel path: several fused buckets launched from post-accumulate-grad hooks while backward
+    is still running must give the same parameters as one process training on the concatenated batch
+    (model without BatchNorm so per-rank and global batches are equivalent), replicas bit-identical."""
+    os.environ["HVD_FUSION_THRESHOLD"] = str(64 << 10)
+    hvd.init()
+    r, n = hvd.rank(), hvd.size()
+
+    def make():
+        torch.manual_seed(3)
+        return torch.nn.Sequential(
+            torch.nn.Conv2d(3, 16, 3, padding=1), torch.nn.ReLU(), torch.nn.Conv2d(16, 32, 3, stride=2, padding=1),
+            torch.nn.ReLU(), torch.nn.Conv2d(32, 64, 3, stride=2, padding=1), torch.nn.ReLU(),
+            torch.nn.AdaptiveAvgPool2d(1), torch.nn.Flatten(), torch.nn.Linear(64, 128), torch.nn.ReLU(),
+            torch.nn.Linear(128, 10))
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    m = keras.TorchModel(make())
+    opt = hvd.DistributedOptimizer(keras.optimizers.SGD(0.05, momentum=0.9))
+    m.compile(optimizer=opt, loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True))
+    rng = np.random.default_rng(11)
+    X = rng.random((n * 8, 16, 16, 3), dtype=np.float32)
+    Y = rng.integers(0, 10, n * 8)
+    m._ensure_built((8, 16, 16, 3))
+    assert opt._fused is not None and len(opt.buckets) >= 3 and opt._hooked, (len(opt.buckets), opt._hooked)
+    ref = keras.TorchModel(make())
+    ref.compile(optimizer=keras.optimizers.SGD(0.05, momentum=0.9),
+                loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True))
+    ref._ensure_built((8 * n, 16, 16, 3))
+    for _ in range(4):
+        m.train_on_batch(X[r * 8:(r + 1) * 8], Y[r * 8:(r + 1) * 8])
+        ref.train_on_batch(X, Y)
+    torch.cuda.synchronize()
+    cs = hvd.allgather_object(int(m.arena.checksum()))
+    assert all(c == cs[0] for c in cs), cs
+    got = torch.cat([w.reshape(-1) for w in map(torch.from_numpy, m.get_weights())])
+    exp = torch.cat([w.reshape(-1) for w in map(torch.from_numpy, ref.get_weights())])
+    print(f"rank {r}: max |w - oracle| = {(got - exp).abs().max().item():.3e}", flush=True)
+    torch.testing.assert_close(got, exp, rtol=1e-3, atol=1e-5)
+    hvd.barrier()
+    print("OK", flush=True)
+
+
 if __name__ == "__main__":
     globals()[os.environ["HVD_TEST_BODY"]]()

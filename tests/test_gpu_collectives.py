@@ -166,7 +166,7 @@ def _run_multi(nproc, body, timeout=300):
 
 
 @pytest.mark.multigpu
-@pytest.mark.parametrize("body", ["collectives", "train_replicas"])
+@pytest.mark.parametrize("body", ["collectives", "train_replicas", "torchmodel_overlap"])
 def test_multi_gpu(body):
     _need_gpu()
     n = torch.cuda.device_count()
