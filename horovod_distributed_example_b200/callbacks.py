@@ -71,6 +71,10 @@ class MetricAverageCallback(Callback):
         if not keys:
             return
         vec = torch.tensor([float(logs[k]) for k in keys], dtype=torch.float64)
+        dev = basics.device()
+        if dev.type == "cuda":
+            # the metric vector rides the same peer-memory allreduce kernels as the gradients
+            vec = vec.to(dev)
         collectives.allreduce_(vec, average=True, name="metric_average")
         for k, v in zip(keys, vec.tolist()):
             logs[k] = v

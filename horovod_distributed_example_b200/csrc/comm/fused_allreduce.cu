@@ -19,6 +19,7 @@
 
 #include <cooperative_groups.h>
 #include <stdio.h>
+#include <string.h>
 
 enum { HVD_ONESHOT = 0, HVD_TWOSHOT = 1, HVD_NVLS = 2 };
 enum { HVD_KIND_NONE = 0, HVD_KIND_SGD = 1, HVD_KIND_ADADELTA = 2, HVD_KIND_ADAM = 3 };
@@ -76,6 +77,9 @@ struct Unroll { static constexpr int value = (VARIANT == HVD_NVLS || NR <= 2) ? 
 template <int VARIANT, int KIND, int NR>
 __global__ void __launch_bounds__(256, 2) hvd_fused_kernel(HvdCommCtx c, HvdFusedArgs a) {
   constexpr int kUnroll = Unroll<VARIANT, NR>::value;
+  // programmatic dependent launch: this grid may have been scheduled while the previous kernel in the
+  // stream was still draining; nothing above touches memory
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const int rank = hvd_rank(c);
   const int N = c.nranks;
   const uint32_t ep = hvd_epoch_load(c, a.slot);
@@ -205,8 +209,15 @@ static cudaError_t launch_vkn(const HvdCommCtx& c, const HvdFusedArgs& a, int ct
     void* args[] = {(void*)&c, (void*)&a};
     return cudaLaunchCooperativeKernel((void*)hvd_fused_kernel<V, K, NR>, dim3(ctas, emu), dim3(threads), args, 0, st);
   }
-  hvd_fused_kernel<V, K, NR><<<ctas, threads, 0, st>>>(c, a);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(threads); cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, hvd_fused_kernel<V, K, NR>, c, a);
 }
 
 template <int V, int K>

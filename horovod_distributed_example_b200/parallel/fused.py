@@ -102,12 +102,25 @@ class FusedReducer:
 
     def run_all(self, grad_buf: int = 0, exit_barrier: int = 1, stream=None) -> None:
         tl = basics.state().timeline
+        if tl is None:
+            for i in range(len(self.buckets)):
+                self.run_bucket(i, grad_buf, exit_barrier, stream)
+            return
+        # HVD_TIMELINE: device durations from CUDA events around each bucket's kernel ("complete" events,
+        # like Horovod's NCCL_ALLREDUCE phase) - costs a sync per step, only when tracing
+        s = stream if stream is not None else torch.cuda.current_stream(self.arena.device)
+        marks = []
         for i in range(len(self.buckets)):
-            if tl is not None:
-                tl.begin(f"grad.bucket{i}", "FUSED_ALLREDUCE_UPDATE")
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s)
             self.run_bucket(i, grad_buf, exit_barrier, stream)
-            if tl is not None:
-                tl.end(f"grad.bucket{i}", "FUSED_ALLREDUCE_UPDATE")
+            e1.record(s)
+            marks.append((i, e0, e1))
+        s.synchronize()
+        t0 = tl.now_us()
+        for i, e0, e1 in marks:
+            dur = int(e0.elapsed_time(e1) * 1e3)
+            tl.complete(f"grad.bucket{i}", f"FUSED_ALLREDUCE_UPDATE_{VARIANT_NAMES[self.variants[i]].upper()}", t0 - dur, dur)
 
     def shard_range(self, i: int, rank: int):
         b, n = self.buckets[i], self.ctx.size
