@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256) head_kernel(HeadParams p) {
   if (lane == 0 && valid) {
     const float loss = -logf(fminf(fmaxf(py, 1e-7f), 1.0f - 1e-7f));     // Keras clips probabilities
     atomicAdd(&p.st->last_loss, p.backward ? loss * invB : loss);        // eval mode reports sums
-    atomicAdd(&p.st->last_correct, am == y ? 1.f : 0.f);
+    atomicAdd(&p.st->last_correct, am == y ? (p.backward ? invB : 1.f) : 0.f);   // training: accuracy fraction; eval: count
   }
   __syncthreads();
   if (!p.backward) return;

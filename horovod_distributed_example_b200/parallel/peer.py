@@ -191,6 +191,7 @@ class PeerContext:
         self._alloc_id = 0
         self.timeout_ns = int(timeout_s * 1e9)
         self._err = torch.zeros(1, dtype=torch.int32).pin_memory() if device.type == "cuda" else None
+        self._err_np = self._err.numpy() if self._err is not None else None      # cheap host-side polling
         if size == 1 and not emulated:
             self.backend = "local"           # single GPU: same kernels, nothing to exchange
         elif not emulated:
@@ -440,9 +441,9 @@ class PeerContext:
 
     def check_error(self) -> None:
         """Raise if an in-kernel barrier timed out (names the peer that did not arrive)."""
-        v = int(self._err[0])
+        v = int(self._err_np[0])
         if v:
-            self._err[0] = 0
+            self._err_np[0] = 0
             raise RuntimeError(f"peer-memory barrier timed out: rank {self.rank} waited for rank "
                                f"{(v & 0xff) - 1} on signal slot {v >> 8} (stalled or failed peer)")
 
