@@ -1,15 +1,12 @@
-"""Equivalent of the reference's ``mnist_keras.py`` on this framework.
+"""MNIST CNN trained data-parallel with Adadelta - the capability of the reference's `mnist_keras.py`
+(same model, batch size, epoch budget, LR scaling, callbacks, rank-0 checkpoints/logs, final
+evaluate + save + reload + serving export) expressed with this framework.
 
-Same structure, same hyper-parameters (batch 128, ceil(12/size) epochs, Adadelta with LR
-1.0*size, BroadcastGlobalVariables, rank-0 ModelCheckpoint + TensorBoard, fit with
-validation, evaluate, rank-0 save / reload / export, every rank prints its score).
-Run single-process (``python examples/mnist_keras.py``) or distributed
-(``python -m horovod_distributed_example_b200.run -np 8 examples/mnist_keras.py``)
-without code changes.  ``HVD_EXAMPLE_SAMPLES`` / ``HVD_EXAMPLE_EPOCHS`` shrink the run
-for smoke tests.
+    python examples/mnist_keras.py                                               # one process
+    python -m horovod_distributed_example_b200.run -np 8 examples/mnist_keras.py  # one process per GPU
+
+`HVD_EXAMPLE_SAMPLES` / `HVD_EXAMPLE_EPOCHS` shrink the run for smoke tests.
 """
-from __future__ import print_function
-
 import math
 import os
 import sys
@@ -19,104 +16,77 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 import horovod_distributed_example_b200 as hvd
 from horovod_distributed_example_b200 import keras
-from horovod_distributed_example_b200.keras import backend as K
-from horovod_distributed_example_b200.keras.datasets import mnist
-from horovod_distributed_example_b200.keras.layers import (Conv2D, Dense, Dropout, Flatten,
-                                                           MaxPooling2D)
-from horovod_distributed_example_b200.keras.models import Sequential, load_model
-from horovod_distributed_example_b200.utils import metrics_sink as metrics
-from horovod_distributed_example_b200.utils import saved_model
+from horovod_distributed_example_b200.utils import metrics_sink, saved_model
 
-metrics.init(sync_tensorboard=True)
+BATCH = 128
+CLASSES = 10
+BASE_EPOCHS = 12
 
-# Gradient path setup
-model_dir, export_dir = hvd.model_paths()
 
-# Initialize (also pins this process to GPU local_rank; no-op on a CPU host)
-hvd.init()
+def load_data():
+    """MNIST as float32 NHWC in [0,1] with one-hot labels (synthetic MNIST-shaped data offline)."""
+    (xtr, ytr), (xte, yte) = keras.datasets.mnist.load_data()
+    limit = int(os.environ.get("HVD_EXAMPLE_SAMPLES", 0))
+    if limit:
+        xtr, ytr = xtr[:limit], ytr[:limit]
+        xte, yte = xte[:max(limit // 4, 256)], yte[:max(limit // 4, 256)]
 
-batch_size = 128
-num_classes = 10
+    def prep(x):
+        return (x.reshape(len(x), 28, 28, 1).astype("float32")) / 255
 
-# adjust number of epochs based on number of GPUs
-epochs = int(os.environ.get("HVD_EXAMPLE_EPOCHS", int(math.ceil(12.0 / hvd.size()))))
+    return (prep(xtr), keras.utils.to_categorical(ytr, CLASSES)), (prep(xte), keras.utils.to_categorical(yte, CLASSES))
 
-img_rows, img_cols = 28, 28
 
-(x_train, y_train), (x_test, y_test) = mnist.load_data()
-n_small = int(os.environ.get("HVD_EXAMPLE_SAMPLES", 0))
-if n_small:
-    x_train, y_train = x_train[:n_small], y_train[:n_small]
-    x_test, y_test = x_test[:max(n_small // 4, 256)], y_test[:max(n_small // 4, 256)]
+def build_model():
+    return keras.Sequential([
+        keras.layers.Conv2D(32, (3, 3), activation="relu", input_shape=(28, 28, 1)),
+        keras.layers.Conv2D(64, (3, 3), activation="relu"),
+        keras.layers.MaxPooling2D((2, 2)),
+        keras.layers.Dropout(0.25),
+        keras.layers.Flatten(),
+        keras.layers.Dense(128, activation="relu"),
+        keras.layers.Dropout(0.5),
+        keras.layers.Dense(CLASSES, activation="softmax"),
+    ])
 
-if K.image_data_format() == 'channels_first':
-    x_train = x_train.reshape(x_train.shape[0], 1, img_rows, img_cols)
-    x_test = x_test.reshape(x_test.shape[0], 1, img_rows, img_cols)
-    input_shape = (1, img_rows, img_cols)
-else:
-    x_train = x_train.reshape(x_train.shape[0], img_rows, img_cols, 1)
-    x_test = x_test.reshape(x_test.shape[0], img_rows, img_cols, 1)
-    input_shape = (img_rows, img_cols, 1)
 
-x_train = x_train.astype('float32')
-x_test = x_test.astype('float32')
-x_train /= 255
-x_test /= 255
-print('x_train shape:', x_train.shape)
-print(x_train.shape[0], 'train samples')
-print(x_test.shape[0], 'test samples')
+def main():
+    metrics_sink.init(sync_tensorboard=True)          # local stand-in for the Gradient metrics sidecar
+    model_dir, export_dir = hvd.model_paths()          # $PS_MODEL_PATH or ./models
+    hvd.init()                                         # also pins this process to GPU <local_rank>
+    world, me = hvd.size(), hvd.rank()
 
-y_train = keras.utils.to_categorical(y_train, num_classes)
-y_test = keras.utils.to_categorical(y_test, num_classes)
+    epochs = int(os.environ.get("HVD_EXAMPLE_EPOCHS", math.ceil(BASE_EPOCHS / world)))   # fewer epochs with more GPUs
+    (x_train, y_train), (x_test, y_test) = load_data()
+    if me == 0:
+        print(f"{len(x_train)} train / {len(x_test)} test samples, shape {x_train.shape[1:]}, {world} rank(s)")
 
-model = Sequential()
-model.add(Conv2D(32, kernel_size=(3, 3), activation='relu', input_shape=input_shape))
-model.add(Conv2D(64, (3, 3), activation='relu'))
-model.add(MaxPooling2D(pool_size=(2, 2)))
-model.add(Dropout(0.25))
-model.add(Flatten())
-model.add(Dense(128, activation='relu'))
-model.add(Dropout(0.5))
-model.add(Dense(num_classes, activation='softmax'))
+    model = build_model()
+    optimizer = hvd.DistributedOptimizer(keras.optimizers.Adadelta(1.0 * world))         # LR scales with ranks
+    model.compile(loss=keras.losses.categorical_crossentropy, optimizer=optimizer, metrics=["accuracy"])
 
-# adjust learning rate based on number of GPUs, then wrap
-opt = keras.optimizers.Adadelta(1.0 * hvd.size())
-opt = hvd.DistributedOptimizer(opt)
+    callbacks = [hvd.callbacks.BroadcastGlobalVariablesCallback(0)]      # every rank starts from rank 0's state
+    if me == 0:                                                          # only rank 0 writes files
+        callbacks += [keras.callbacks.ModelCheckpoint(os.path.join(model_dir, "checkpoint-{epoch}.h5")),
+                      keras.callbacks.TensorBoard(log_dir=os.path.join(model_dir, "eval"), update_freq="batch")]
 
-model.compile(loss=keras.losses.categorical_crossentropy, optimizer=opt, metrics=['accuracy'])
+    model.fit(x_train, y_train, batch_size=BATCH, epochs=epochs, callbacks=callbacks,
+              verbose=int(me == 0), validation_data=(x_test, y_test))
+    loss, accuracy = model.evaluate(x_test, y_test, verbose=0)
 
-callbacks = [
-    # broadcast initial variable states from rank 0 to all other processes
-    hvd.callbacks.BroadcastGlobalVariablesCallback(0),
-]
+    if me == 0:
+        final_path = os.path.join(model_dir, "keras-sample-model.h5")
+        model.save(final_path)
+        print(f"Model saved to {final_path}")
+        keras.backend.set_learning_phase(0)
+        served = keras.load_model(final_path)
+        saved_model.export(served, os.path.join(export_dir, time.strftime("%Y%m%d-%H%M%S")),
+                           inputs={"input": None}, outputs={"prob": None})
+        print("acceptance:", metrics_sink.check("tensorflow:loss", "0.0..0.3", "mean"))
 
-# save checkpoints only on worker 0
-if hvd.rank() == 0:
-    checkpoint_path = os.path.join(model_dir, 'checkpoint-{epoch}.h5')
-    logs_path = os.path.join(model_dir, 'eval')
-    callbacks.append(keras.callbacks.ModelCheckpoint(checkpoint_path))
-    callbacks.append(keras.callbacks.TensorBoard(log_dir=logs_path, update_freq='batch'))
+    print("Test loss:", loss)            # every rank reports its own evaluation, as the reference does
+    print("Test accuracy:", accuracy)
 
-model.fit(x_train, y_train,
-          batch_size=batch_size,
-          callbacks=callbacks,
-          epochs=epochs,
-          verbose=1 if hvd.rank() == 0 else 0,
-          validation_data=(x_test, y_test))
-score = model.evaluate(x_test, y_test, verbose=0)
 
-if hvd.rank() == 0:
-    exported_model_path = os.path.join(model_dir, 'keras-sample-model.h5')
-    model.save(exported_model_path)
-    print("Model saved to {}".format(exported_model_path))
-
-    K.set_learning_phase(0)
-    new_model = load_model(exported_model_path)
-
-    # serving export: input -> prob signature under <export_dir>/<timestamp>
-    saved_model.export(new_model, os.path.join(export_dir, time.strftime("%Y%m%d-%H%M%S")),
-                       inputs={'input': None}, outputs={'prob': None})
-    print("CI check:", metrics.check("tensorflow:loss", "0.0..0.3", "mean"))
-
-print('Test loss:', score[0])
-print('Test accuracy:', score[1])
+if __name__ == "__main__":
+    main()

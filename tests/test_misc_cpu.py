@@ -136,12 +136,12 @@ def test_launcher_env_contract(tmp_path):
 
 def test_workflow_runner_ci_check(tmp_path):
     """The reference's only acceptance test (GradientCI: mean tensorflow:loss in 0.0..0.3,
-    .ps_project/config.yaml:8-11) runs in-repo: tools/run_workflow.py launches the sample through
+    reference .ps_project/config.yaml:8-11) runs in-repo: tools/run_workflow.py launches the sample through
     hvdrun (2 CPU ranks here) and evaluates the check on the recorded metrics."""
     env = dict(os.environ, CUDA_VISIBLE_DEVICES="", HVD_EXAMPLE_SAMPLES="1536", HVD_EXAMPLE_EPOCHS="6",
                PS_MODEL_PATH=str(tmp_path), KERAS_HOME=str(tmp_path / "keras"), OMP_NUM_THREADS="2")
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "run_workflow.py"), "--np", "2"],
                        cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    assert '"passed": true' in r.stdout and "tensorflow:loss" in r.stdout
+    assert '"passed": true' in r.stdout and '"metric": "loss"' in r.stdout
     assert os.path.exists(tmp_path / "horovod-mnist" / "checkpoint-1.h5")

@@ -1,71 +1,73 @@
-"""Run a `.ps_project/config.yaml` workflow locally: launch each step's master command and evaluate
-the metric checks on what the run recorded - the stand-in for Gradient's `experiment.run_mpi_multi_node`
-+ GradientCI check (reference .ps_project/config.yaml:5-11, distributed-keras-sample.yaml:8).
+"""Run `.ps_project/workflow.yaml` locally: launch the experiment through hvdrun and evaluate the
+acceptance checks on the scalars the run recorded.  This is the in-repo equivalent of the reference's
+Gradient multi-node experiment plus its GradientCI metric check (loss must average 0.0..0.3).
 
-    python tools/run_workflow.py [--config .ps_project/config.yaml] [--np N] [--env K=V ...]
+    python tools/run_workflow.py [--workflow .ps_project/workflow.yaml] [--np N] [--env K=V ...]
 
-Exit code 0 iff every step exits 0 and every check passes.
+Exit code 0 iff the experiment exits 0 and every check passes.
 """
 import argparse
 import json
 import os
-import shlex
 import subprocess
 import sys
 
 import yaml
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# scalar tags a check on "<name>" may be satisfied by, most specific first
+TAGS = {"loss": ("epoch_loss", "batch_loss", "loss"), "accuracy": ("epoch_accuracy", "batch_accuracy", "accuracy")}
+AGG = {"mean": lambda v: sum(v) / len(v), "min": min, "max": max, "last": lambda v: v[-1]}
 
 
-def evaluate(metrics_path, checks):
-    vals = {}
-    if os.path.exists(metrics_path):
-        for line in open(metrics_path):
-            r = json.loads(line)
-            vals.setdefault(r["tag"], []).append(r["value"])
-    alias = {"tensorflow:loss": ("epoch_loss", "batch_loss", "loss")}
-    out = []
-    for metric, spec in (checks or {}).items():
-        lo, hi = (float(x) for x in spec["target"].split(".."))
-        series = next((vals[t] for t in alias.get(metric, (metric,)) if vals.get(t)), [])
-        if not series:
-            out.append({"metric": metric, "passed": False, "reason": "no values recorded"})
-            continue
-        agg = {"mean": sum(series) / len(series), "min": min(series), "max": max(series),
-               "last": series[-1]}[spec.get("aggregate", "mean")]
-        out.append({"metric": metric, "aggregate": spec.get("aggregate", "mean"), "value": agg,
-                    "target": spec["target"], "passed": lo <= agg <= hi})
+def read_scalars(path):
+    out = {}
+    if os.path.exists(path):
+        with open(path) as f:
+            for line in f:
+                rec = json.loads(line)
+                out.setdefault(rec["tag"], []).append(rec["value"])
     return out
+
+
+def run_checks(scalars, checks):
+    results = []
+    for chk in checks or []:
+        series = next((scalars[t] for t in TAGS.get(chk["metric"], (chk["metric"],)) if scalars.get(t)), None)
+        if not series:
+            results.append({"metric": chk["metric"], "passed": False, "reason": "no values recorded"})
+            continue
+        value = AGG[chk.get("aggregate", "mean")](series)
+        results.append({"metric": chk["metric"], "aggregate": chk.get("aggregate", "mean"), "value": value,
+                        "range": [chk["min"], chk["max"]], "passed": chk["min"] <= value <= chk["max"]})
+    return results
 
 
 def main(argv=None):
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", default=os.path.join(ROOT, ".ps_project", "config.yaml"))
-    ap.add_argument("--np", type=int, default=None, help="override the process count in the master command")
+    ap.add_argument("--workflow", default=os.path.join(ROOT, ".ps_project", "workflow.yaml"))
+    ap.add_argument("--np", type=int, default=None, help="override the experiment's process count")
     ap.add_argument("--env", action="append", default=[])
     a = ap.parse_args(argv)
-    cfg = yaml.safe_load(open(a.config))
-    ok = True
-    for wname, wf in cfg.get("workflows", {}).items():
-        metrics_path = os.path.join(ROOT, "metrics.jsonl")
-        if os.path.exists(metrics_path):
-            os.remove(metrics_path)
-        for step in wf.get("steps", []):
-            params = yaml.safe_load(open(os.path.join(ROOT, step["paramsFile"])))
-            cmd = shlex.split(params["masterCommand"])
-            if a.np is not None and "-np" in cmd:
-                cmd[cmd.index("-np") + 1] = str(a.np)
-            env = dict(os.environ, HVD_METRICS_PATH=metrics_path)
-            env.update(dict(e.split("=", 1) for e in a.env))
-            print(f"[workflow {wname}] step {step['name']}: {' '.join(cmd)}", flush=True)
-            rc = subprocess.run(cmd, cwd=ROOT, env=env).returncode
-            if rc != 0:
-                print(f"[workflow {wname}] step failed with exit code {rc}")
-                ok = False
-        for res in evaluate(metrics_path, wf.get("checks")):
-            print(f"[workflow {wname}] check {json.dumps(res)}")
-            ok = ok and res["passed"]
+    wf = yaml.safe_load(open(a.workflow))
+    exp = yaml.safe_load(open(os.path.join(ROOT, wf["run"]["experiment"])))
+    metrics_path = os.path.join(ROOT, "metrics.jsonl")
+    if os.path.exists(metrics_path):
+        os.remove(metrics_path)
+    cmd = [sys.executable, "-m", "horovod_distributed_example_b200.run", "-np", str(a.np or exp["processes"])]
+    for item in exp.get("export", []):
+        cmd += ["-x", item]
+    cmd.append(exp["script"])
+    env = dict(os.environ, HVD_METRICS_PATH=metrics_path)
+    env.update(dict(e.split("=", 1) for e in a.env))
+    print(f"[{wf['name']}] {' '.join(cmd)}", flush=True)
+    rc = subprocess.run(cmd, cwd=ROOT, env=env).returncode
+    ok = rc == 0
+    if rc != 0:
+        print(f"[{wf['name']}] experiment failed with exit code {rc}")
+    for res in run_checks(read_scalars(metrics_path), wf.get("accept")):
+        print(f"[{wf['name']}] check {json.dumps(res)}")
+        ok = ok and res["passed"]
     return 0 if ok else 1
 
 
