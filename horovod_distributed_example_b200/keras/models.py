@@ -89,6 +89,14 @@ class _HostStager:
         self._flip ^= 1
 
 
+class _Resolved:
+    def __init__(self, value):
+        self._v = value
+
+    def result(self):
+        return self._v
+
+
 class Model:
     """Trainer front end.  Subclasses provide ``_weight_specs`` and ``_forward``."""
 
@@ -239,6 +247,18 @@ class Model:
         if self._metric_accuracy:
             out.append(float(acc))
         return out if len(out) > 1 else out[0]
+
+    def train_on_batch_async(self, x, y):
+        """Non-blocking ``train_on_batch``: enqueues the host->device copy of this batch, the step and the
+        device->host read of its (loss, accuracy), and returns a handle whose ``result()`` waits for that
+        step only.  Resolving handles one step late lets the copy of batch t+1 overlap the compute of
+        step t (the fused engine double-buffers its inputs); other backends resolve immediately."""
+        x, y = _to_numpy(x), _to_numpy(y)
+        self._ensure_built(x.shape)
+        if hasattr(self._backend, "train_host_batch_async"):
+            return self._backend.train_host_batch_async(x, y)
+        out = self.train_on_batch(x, y)
+        return _Resolved(tuple(out) if isinstance(out, list) else (out, None))
 
     def test_on_batch(self, x, y):
         x, y = _to_numpy(x), _to_numpy(y)

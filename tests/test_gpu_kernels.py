@@ -303,3 +303,21 @@ def test_dense_forward_splitk_with_caller_scratch(M, N, K, relu, ks):
     ref = F.relu(ref) if relu else ref
     assert _rel(y, ref) < 3e-3
     assert (scratch == 0).all()
+
+
+def test_async_host_steps_match_blocking_steps():
+    """train_on_batch_async (pipelined H2D / D2H, inputs double-buffered) gives the same losses and
+    weights as blocking train_on_batch on the same batches (dropout off, same seed)."""
+    _lib()
+    hvd, build = _models(0.0, 0.0, "adadelta")
+    rng = np.random.default_rng(1)
+    X = rng.random((6, B, 28, 28, 1), dtype=np.float32)
+    Y = rng.integers(0, 10, (6, B))
+    a, b = build(), build()
+    la = [a.train_on_batch(X[i], Y[i])[0] for i in range(6)]
+    hs = [b.train_on_batch_async(X[i], Y[i]) for i in range(6)]       # all six enqueued before any is read
+    lb = [h.result()[0] for h in hs]
+    np.testing.assert_allclose(la, lb, rtol=2e-3, atol=1e-4)          # red.add ordering differs run to run
+    for wa, wb in zip(a.get_weights(), b.get_weights()):
+        np.testing.assert_allclose(wa, wb, rtol=0, atol=5e-3)
+    hvd.shutdown()
