@@ -15,8 +15,6 @@ Dispatch:
 """
 from __future__ import annotations
 
-import io
-import pickle
 from typing import Iterable, Optional
 
 import torch
@@ -244,9 +242,3 @@ def broadcast_parameters(params, root_rank: int = 0) -> None:
     for name, p in items:
         if isinstance(p, torch.Tensor):
             broadcast_(p.data, root_rank, name=f"broadcast.{name}")
-
-
-def _dumps(obj) -> bytes:  # small helper used by tests
-    b = io.BytesIO()
-    pickle.dump(obj, b)
-    return b.getvalue()

@@ -188,5 +188,5 @@ class ArrayBatcher:
             if order is None:
                 yield tuple(a[s:s + self.batch_size] for a in self.arrays)
             else:
-                idx = np.sort(order[s:s + self.batch_size]) if False else order[s:s + self.batch_size]
+                idx = order[s:s + self.batch_size]
                 yield tuple(a[idx] for a in self.arrays)

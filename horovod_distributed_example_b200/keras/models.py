@@ -327,9 +327,12 @@ class Model:
                     break
                 n = len(xb)
                 cl.on_batch_begin(step, {"batch": step, "size": n})
-                xd, yd = st(xb, torch.float32), st(yb)
-                st.next_step()
-                loss, acc = be.train_step(xd, yd)
+                if hasattr(be, "train_host_lazy"):
+                    loss, acc = be.train_host_lazy(xb, yb)       # engine stages the batch itself (pipelined H2D)
+                else:
+                    xd, yd = st(xb, torch.float32), st(yb)
+                    st.next_step()
+                    loss, acc = be.train_step(xd, yd)
                 loss_sum += loss.detach().to(torch.float64) * n
                 seen += n
                 logs = {"batch": step, "size": n, "loss": loss}
