@@ -112,6 +112,8 @@ def init(comm=None, *, backend: Optional[str] = None, device: Optional[str] = No
     _state.cross_size = max(size // max(local_size, 1), 1)
     _state.config = cfg
     _setup_logging(cfg.log_level)
+    from .utils import nvtx
+    nvtx.configure(cfg.nvtx, rank=rank, level=cfg.log_level)
 
     want_cuda = torch.cuda.is_available() if device is None else device.startswith("cuda")
     if want_cuda:

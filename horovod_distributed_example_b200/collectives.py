@@ -21,6 +21,7 @@ import torch
 
 from . import basics
 from .basics import _state, _require_init
+from .utils import nvtx
 
 # Horovod reduce-op constants (later Horovod versions; `average=` is the 0.18 spelling).
 Average = "average"
@@ -92,6 +93,7 @@ def allreduce_(tensor: torch.Tensor, average: bool = True, name: Optional[str] =
     tl = _state.timeline
     if tl is not None:
         tl.begin(name or "allreduce", "ALLREDUCE")
+    nvtx.push(name or "hvd.allreduce")
     try:
         if _use_peer(tensor):
             from .parallel import peer
@@ -109,6 +111,7 @@ def allreduce_(tensor: torch.Tensor, average: bool = True, name: Optional[str] =
             if work_t is not tensor:
                 tensor.copy_(work_t)
     finally:
+        nvtx.pop()
         if tl is not None:
             tl.end(name or "allreduce", "ALLREDUCE")
     return tensor
@@ -156,6 +159,7 @@ def broadcast_(tensor: torch.Tensor, root_rank: int = 0, name: Optional[str] = N
     tl = _state.timeline
     if tl is not None:
         tl.begin(name or "broadcast", "BROADCAST")
+    nvtx.push(name or "hvd.broadcast")
     try:
         if _use_peer(tensor):
             from .parallel import peer
@@ -170,6 +174,7 @@ def broadcast_(tensor: torch.Tensor, root_rank: int = 0, name: Optional[str] = N
                 dist.broadcast(tmp, src=root_rank, group=group)
                 tensor.copy_(tmp)
     finally:
+        nvtx.pop()
         if tl is not None:
             tl.end(name or "broadcast", "BROADCAST")
     return tensor

@@ -66,6 +66,8 @@ class Config:
     log_level: str = "WARNING"
     #: every N steps compare a parameter checksum across ranks (0 = off).
     debug_checksum: int = 0
+    debug_poison: bool = False         # NaN-fill consumed gradient ranges after every update (stale-read trap)
+    nvtx: bool = False                 # NVTX ranges around steps / buckets / collectives
     #: "rank:step" - that rank skips its collective at that step (tests the watchdog).
     fault_inject: Optional[str] = None
     #: seconds an in-kernel barrier may spin before it gives up and flags an error.
@@ -92,6 +94,8 @@ class Config:
         c.timeline_mark_cycles = _env_bool("TIMELINE_MARK_CYCLES")
         c.log_level = (_env("LOG_LEVEL", c.log_level) or "WARNING").upper()
         c.debug_checksum = _env_int("DEBUG_CHECKSUM", 0)
+        c.debug_poison = _env_int("DEBUG_POISON", 0) != 0
+        c.nvtx = _env_int("NVTX", 0) != 0
         c.fault_inject = _env("FAULT_INJECT")
         c.stall_check_time = _env_float("STALL_CHECK_TIME_SECONDS", c.stall_check_time)
         c.stall_shutdown_time = _env_float("STALL_SHUTDOWN_TIME_SECONDS", c.stall_shutdown_time)

@@ -20,6 +20,8 @@
 #include <mutex>
 #include <string>
 
+void hvd_logf(int lvl, const char* fmt, ...);   // diag.cpp
+
 namespace {
 
 thread_local std::string g_symm_err;
@@ -105,6 +107,7 @@ int fail(const char* what, CUresult r) {
   const char* s = nullptr;
   if (g_drv.p_cuGetErrorString) g_drv.p_cuGetErrorString(r, &s);
   g_symm_err = std::string(what) + ": " + (s ? s : "unknown CUDA error") + " (" + std::to_string((int)r) + ")";
+  hvd_logf(1 /*DEBUG: callers fall back to CUDA IPC and report at their own level*/, "symm: %s", g_symm_err.c_str());
   return -(int)r - 1000;
 }
 

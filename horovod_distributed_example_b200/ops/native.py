@@ -174,6 +174,14 @@ def _declare_core(lib):
     _sig(lib, "hvd_tl_event", c_i32, [c_vp, c_cp, c_cp, ctypes.c_char, c_i64, c_i64])
     _sig(lib, "hvd_tl_now_us", c_i64, [c_vp])
     _sig(lib, "hvd_tl_close", None, [c_vp])
+    _sig(lib, "hvd_log_set_level", None, [c_i32])
+    _sig(lib, "hvd_log_level", c_i32, [])
+    _sig(lib, "hvd_log_set_rank", None, [c_i32])
+    _sig(lib, "hvd_log_parse_level", c_i32, [c_cp])
+    _sig(lib, "hvd_log", None, [c_i32, c_cp])
+    _sig(lib, "hvd_nvtx_push", c_i32, [c_cp])
+    _sig(lib, "hvd_nvtx_pop", c_i32, [])
+    _sig(lib, "hvd_nvtx_mark", None, [c_cp])
     _sig(lib, "hvd_h5_last_error", c_cp, [])
     _sig(lib, "hvd_h5w_create", c_vp, [])
     _sig(lib, "hvd_h5w_free", None, [c_vp])

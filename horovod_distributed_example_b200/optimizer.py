@@ -150,11 +150,20 @@ class _DistributedMixin:
             else:
                 self._fused.run_all()
             self._push_hyper()
-            cfg = basics.config()
-            if cfg.debug_checksum and self.iterations % cfg.debug_checksum == 0:
-                self._check_replicas(arena)
+            self._debug_after_step(arena, 0)
             return
         super().apply_gradients(arena)
+        self._debug_after_step(arena, 0)
+
+    def _debug_after_step(self, arena, which: int = 0) -> None:
+        """replica checksum every HVD_DEBUG_CHECKSUM steps; HVD_DEBUG_POISON=1 NaN-fills
+        the gradient ranges the update has just consumed, so a later kernel that reads a gradient nobody
+        rewrote (stale data that would otherwise look plausible) turns the loss into NaN at once."""
+        cfg = basics.config()
+        if cfg.debug_checksum and self.iterations % cfg.debug_checksum == 0:
+            self._check_replicas(arena)
+        if cfg.debug_poison:
+            arena.poison_grads(which)
 
 
 def _check_replicas_impl(arena):

@@ -133,6 +133,13 @@ class ParamArena:
         idx = torch.arange(1, w.numel() + 1, device=w.device, dtype=torch.int64)
         return ((w * (idx % 8191 + 1)).sum()) & 0x7FFFFFFFFFFF
 
+    def poison_grads(self, which: int = 0) -> None:
+        """NaN-fill every tensor's range of gradient buffer ``which`` (debug; padding is left alone because
+        the update kernels run over it and the parameter checksum covers it)."""
+        buf = self.grad_bufs[which]
+        for s in self.specs:
+            buf[s.offset:s.offset + s.numel].fill_(float("nan"))
+
     def resize_slots(self, n_slots: int, allocator=None, double_grads: Optional[bool] = None) -> "ParamArena":
         """Return a new arena with ``n_slots`` optimizer slots (optionally in memory from ``allocator``),
         carrying params and existing slots over."""

@@ -12,6 +12,8 @@ from typing import List, Optional
 
 import torch
 
+from ..utils import nvtx
+
 from .. import basics
 from . import peer as peer_mod
 from .peer import HvdFusedArgs, NVLS, ONESHOT, TWOSHOT, VARIANT_NAMES
@@ -98,7 +100,10 @@ class FusedReducer:
         return a
 
     def run_bucket(self, i: int, grad_buf: int = 0, exit_barrier: int = 1, stream=None, hyper_row=None) -> None:
+        if nvtx.enabled():
+            nvtx.push(f"hvd.bucket{i}.{VARIANT_NAMES[self.variants[i]]}")
         self.ctx.launch_fused(self.buf, self._args(i, grad_buf, exit_barrier, hyper_row), self.ctas[i], stream=stream)
+        nvtx.pop()
 
     def run_all(self, grad_buf: int = 0, exit_barrier: int = 1, stream=None) -> None:
         tl = basics.state().timeline

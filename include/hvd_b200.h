@@ -38,6 +38,18 @@ int hvd_tl_event(void* h, const char* tensor, const char* activity, char ph, int
 int64_t hvd_tl_now_us(void* h);
 void hvd_tl_close(void* h);
 
+/* Levelled logging (Horovod logging.cc; HVD_LOG_LEVEL / HOROVOD_LOG_LEVEL read on first use) and NVTX ranges
+ * (header-only NVTX3: free unless a profiler is attached). */
+enum { HVD_LOG_TRACE = 0, HVD_LOG_DEBUG = 1, HVD_LOG_INFO = 2, HVD_LOG_WARNING = 3, HVD_LOG_ERROR = 4, HVD_LOG_FATAL = 5 };
+void hvd_log_set_level(int lvl);
+int hvd_log_level(void);
+void hvd_log_set_rank(int rank);
+int hvd_log_parse_level(const char* s);
+void hvd_log(int lvl, const char* msg);
+int hvd_nvtx_push(const char* name);
+int hvd_nvtx_pop(void);
+void hvd_nvtx_mark(const char* name);
+
 /* Minimal HDF5 writer/reader - the checkpoint-{epoch}.h5 files of ModelCheckpoint / model.save /
  * load_model (reference mnist_keras.py:101-104,118-119,124).  dtype: 0 f32, 1 i64, 2 f64, 3 i32, 4 string. */
 const char* hvd_h5_last_error(void);

@@ -266,8 +266,9 @@ def test_engine_matches_torch_oracle_without_dropout(opt_name, monkeypatch):
     hvd.shutdown()
 
 
-def test_engine_trains_with_dropout_and_partial_batch():
+def test_engine_trains_with_dropout_and_partial_batch(monkeypatch):
     _lib()
+    monkeypatch.setenv("HVD_DEBUG_GUARD", "1")      # red zones around every activation buffer
     hvd, build = _models(0.25, 0.5, "adadelta")
     from horovod_distributed_example_b200 import keras
     (x, y), (xt, yt) = keras.datasets.synthetic_mnist(1024 + 96, 256)
@@ -278,6 +279,8 @@ def test_engine_trains_with_dropout_and_partial_batch():
     assert type(m._backend).__name__ == "MnistEngine"
     assert h.history["loss"][-1] < 0.3 < h.history["loss"][0]            # the reference's CI range
     assert h.history["val_accuracy"][-1] > 0.9
+    assert m.predict(xt[:37]).shape == (37, 10)
+    assert m._backend.check_guards()                 # no kernel wrote outside its buffer (full and partial batches)
     hvd.shutdown()
 
 

@@ -145,3 +145,46 @@ def test_workflow_runner_ci_check(tmp_path):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert '"passed": true' in r.stdout and '"metric": "loss"' in r.stdout
     assert os.path.exists(tmp_path / "horovod-mnist" / "checkpoint-1.h5")
+
+
+def test_native_logger_levels_and_nvtx_noop():
+    """The C++ logger filters by HVD_LOG_LEVEL and prefixes the rank; NVTX calls are harmless with no
+    profiler attached."""
+    code = (
+        "from horovod_distributed_example_b200.utils import nvtx\n"
+        "nvtx.configure(True, rank=3, level='INFO')\n"
+        "nvtx.native_log(1, 'dbg-hidden'); nvtx.native_log(2, 'info-shown'); nvtx.native_log(4, 'err-shown')\n"
+        "with nvtx.range('outer'):\n"
+        "    nvtx.mark('m')\n"
+        "print('done')\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stderr
+    assert "dbg-hidden" not in r.stderr
+    assert "[hvd 3] INFO info-shown" in r.stderr and "[hvd 3] ERROR err-shown" in r.stderr
+
+
+def test_debug_poison_marks_consumed_gradients(hvd_single, monkeypatch):
+    """HVD_DEBUG_POISON: after an update the gradient ranges are NaN (padding untouched) and training still
+    works because every step rewrites them before they are read."""
+    import torch
+    import horovod_distributed_example_b200 as hvd
+    hvd.basics.state().config.debug_poison = True
+    try:
+        rng = np.random.default_rng(0)
+        x = rng.normal(size=(64, 12)).astype(np.float32)
+        y = (x[:, 0] > 0).astype(np.int64)
+        m = keras.Sequential([keras.layers.Dense(8, activation="relu", input_shape=(12,)),
+                              keras.layers.Dense(2, activation="softmax")])
+        m.compile(loss="sparse_categorical_crossentropy", optimizer=hvd.DistributedOptimizer(keras.optimizers.Adam(0.01)),
+                  metrics=["accuracy"])
+        l0 = m.train_on_batch(x, y)[0]
+        g = m.arena.grad_bufs[0]
+        for s in m.arena.specs:
+            assert torch.isnan(g[s.offset:s.offset + s.numel]).all()
+        for _ in range(30):
+            l1 = m.train_on_batch(x, y)[0]
+        assert np.isfinite(l1) and l1 < l0
+        assert torch.isfinite(m.arena.params).all()
+    finally:
+        hvd.basics.state().config.debug_poison = False
