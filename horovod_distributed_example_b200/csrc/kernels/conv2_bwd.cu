@@ -1,13 +1,21 @@
 // conv2 backward on tcgen05 / TMEM / TMA (reference layer: Conv2D(64,(3,3)) at mnist_keras.py:75).
 //
 // dgrad  da1[b,y,x,ci] = relu'(a1) * sum_{kh,kw,co} dY2[b,y-kh,x-kw,co] * W2[kh,kw,ci,co]
-//        implicit GEMM: M = 16x8 output pixels per tile, N = 32 ci, K = 9 taps x 64 co.  A = ONE haloed
-//        4-D TMA box of dY2 per channel half ({32 co, 10 w, 18 h}) at NEGATIVE offsets - the "full"
-//        convolution's zero padding is TMA out-of-bounds fill, no padded copy exists - and the 9 taps
-//        are row-shifted descriptors into that tile (group stride 10 rows), 5.9x less L2 traffic than
-//        a box per tap.
-//        B = W2[tap] as [ci][co] (co contiguous = K-major), whole kernel resident in smem.
-//        Epilogue applies conv1's ReLU mask and stores da1.
+//        A 128 x N x 8 TF32 MMA costs ~77 cycles for every N <= 128 (profiles/mma_probe.json), so the
+//        "one MMA per tap with N = 32 ci" form wastes 3/4 of the tensor core.  Instead the three kw taps
+//        ride in N and only kh is a row shift of A:
+//            Z[p][(kw,ci)] = sum_{kh,co} dY2row[p - 26*kh][co] * W2[kh][kw][ci][co]      N = 96, K = 3 x 64
+//            da1[p][ci]    = Z[p][0,ci] + Z[p-1][1,ci] + Z[p-2][2,ci]                     (epilogue)
+//        p runs over a 26-wide raster of the 26x26 output; dY2 columns 24,25 and rows outside 0..23 are
+//        TMA out-of-bounds zero fill, so the x-1 / x-2 neighbours at a row start read zeros and no
+//        predicates are needed.  A = one haloed 4-D TMA box ({32 co, 26 w, 8 h}) per channel half; the
+//        three kh are row-shifted descriptors into it (start at any row: the tensor core swizzles on
+//        absolute smem address bits).  M tiles are 128 consecutive raster positions with a stride of
+//        126, so the two neighbours a tile's first outputs need are that tile's own lanes 0 and 1.
+//        24 MMAs per 126 outputs instead of 72 per 128 (of which a third were tile padding).
+//        B = W2 as [(kw,ci)][co] per (kh, half) (co contiguous = K-major), whole kernel resident in smem.
+//        Epilogue: kw reduction by warp shuffles (+ a 3-vector exchange across warp boundaries), conv1's
+//        ReLU mask, optional da1 store, and the staging tiles of the fused conv1 weight gradient.
 //
 // wgrad  dW2[kh,kw,ci,co] = sum_{b,oy,ox} a1[b,oy+kh,ox+kw,ci] * dY2[b,oy,ox,co]
 //        the reduction runs over pixels, so BOTH operands are MN-major: A[(tap,ci)][pixel] and
@@ -27,15 +35,19 @@ using namespace mnist;
 // ============================================================================ dgrad
 namespace dg {
 constexpr int STAGES = 3;
-constexpr int A_STAGE = 24 * 1024;          // box {32 co, 10 w, 18 h, 1 n} = 180 rows x 128 B (23,040 B)
-constexpr int A_TX = 180 * 128;
+constexpr int BOX_W = 26, BOX_H = 8;        // haloed dY2 box: 26 columns (24 + 2 zero), 8 rows (6 + 2 halo)
+constexpr int A_STAGE = BOX_W * BOX_H * 128;   // 208 rows x 128 B = 26,624 B (a multiple of 1024)
+constexpr int A_TX = A_STAGE;
 constexpr int W_BYTES = 18 * 4096;
 constexpr int STG_BYTES = 32 * 1024;        // fused conv1-wgrad staging: im2col(x) tile 16 KB + da1 tile 16 KB
-constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 2 * STG_BYTES + 1024 /*base align*/ + 1024 /*barriers*/ + 256;
-constexpr int TMEM_COLS = 128;              // 2 dgrad stages x 32 columns + 32 columns for the conv1 wgrad accumulator
-constexpr int TH = 16, TW = 8;              // output tile: 16 rows x 8 columns = 128 pixels
-constexpr int TILES_X = 4;                  // 26 = 3*8 + 2 -> 4 column tiles; 26 = 16 + 10 -> 2 row tiles
-constexpr uint32_t SBO_HALO = 10 * 128;
+constexpr int XCH_BYTES = 2 * 4 * 96 * 4;   // kw-reduction exchange across warp boundaries, double-buffered
+constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 2 * STG_BYTES + XCH_BYTES + 1024 /*base align*/ + 1024 /*barriers*/ + 256;
+constexpr int TMEM_COLS = 256;              // 2 dgrad stages x 96 columns + 32 columns for the conv1 wgrad accumulator
+constexpr int ACC_N = 96;                   // (kw, ci)
+constexpr int W1_COL = 2 * ACC_N;
+constexpr int TILE_STRIDE = 126;            // raster positions owned by a tile (lanes 0,1 only donate, except in tile 0)
+constexpr int TILES_PER_IMG = 6;            // 5*126 + 128 = 758 >= 676
+constexpr int NPOS = H1 * H1;               // 676
 
 struct Params {
   int B, n_tiles;
@@ -69,6 +81,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   uint64_t* w1done = stge + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w1done + 1);
   uint8_t* sStg = sA + STAGES * A_STAGE + 1024;  // the barrier block owns the 1 KB in between (keeps 1024 B alignment)
+  float* sXch = reinterpret_cast<float*>(sStg + 2 * STG_BYTES);
   const bool fuse_w1 = p.x != nullptr;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -94,29 +107,32 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   if (warp == 0) {
     if (tc::elect_one()) {
       tc::mbar_expect_tx(wfull, W_BYTES);
+      // smem W layout: block (kh, half, kw) of [32 ci][32 co] -> for a fixed (kh, half) the 96 rows (kw, ci)
+      // are contiguous = one N = 96 K-major operand
       for (int t = 0; t < 9; t++)
-        for (int h = 0; h < 2; h++) tc::tma_load_2d(sW + (t * 2 + h) * 4096, &tmW, wfull, 32 * h, t * 32);
+        for (int h = 0; h < 2; h++)
+          tc::tma_load_2d(sW + (((t / 3) * 2 + h) * 3 + (t % 3)) * 4096, &tmW, wfull, 32 * h, t * 32);
       int it = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-        const int b = tile / 8, ty = (tile % 8) / TILES_X, tx = tile % TILES_X;
+        const int b = tile / TILES_PER_IMG, ybase = ((tile % TILES_PER_IMG) * TILE_STRIDE) / H1;
         for (int half = 0; half < 2; half++, it++) {
           const int s = it % STAGES;
           tc::mbar_wait(&empty[s], ((it / STAGES) & 1) ^ 1);
           tc::mbar_expect_tx(&full[s], A_TX);
-          // haloed dY2 tile: origin (x0-2, y0-2); everything outside 24x24 is TMA zero fill = the
-          // "full" convolution's padding
-          tc::tma_load_4d(sA + s * A_STAGE, &tmG, &full[s], 32 * half, tx * TW - 2, ty * TH - 2, b);
+          // haloed dY2 rows ybase-2 .. ybase+5, columns 0..25: everything outside 24x24 is TMA zero fill
+          // (= the "full" convolution's padding and the raster's two pad columns)
+          tc::tma_load_4d(sA + s * A_STAGE, &tmG, &full[s], 32 * half, 0, ybase - 2, b);
         }
       }
     }
   } else if (warp == 1) {
     if (tc::elect_one()) {
-      constexpr uint32_t idesc = tc::make_idesc_tf32(128, 32, 0, 0);
+      constexpr uint32_t idesc = tc::make_idesc_tf32(128, ACC_N, 0, 0);
       constexpr uint32_t idesc_w1 = tc::make_idesc_tf32(128, 32, 1, 1);
       const uint64_t dW0 = tc::desc_kmajor(tc::smem_u32(sW));
       // Fused conv1 weight gradient: dW1[tap][c] (+ db1 as "tap" 9) = sum over the tile's 128 pixels of
       // im2col(x)[pixel][tap] * da1[pixel][c].  Both staging tiles are [pixel][32] rows written by the
-      // epilogue = MN-major operands with K = pixels: 16 MMAs (K=8) per tile into TMEM columns 64..95.
+      // epilogue = MN-major operands with K = pixels: 16 MMAs (K=8) per tile into TMEM columns W1_COL..+31.
       auto w1_mma = [&](int tj) {
         const int sb = tj & 1;
         tc::mbar_wait(&stgf[sb], (tj >> 1) & 1);
@@ -126,7 +142,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         const uint64_t dB = tc::make_smem_desc(st + 16384, 0, 512, 1);
 #pragma unroll
         for (int ks = 0; ks < 16; ks++)
-          tc::mma_tf32(tmem + 64, tc::desc_advance(dA, ks * 1024), tc::desc_advance(dB, ks * 1024), idesc_w1, (tj | ks) != 0);
+          tc::mma_tf32(tmem + W1_COL, tc::desc_advance(dA, ks * 1024), tc::desc_advance(dB, ks * 1024), idesc_w1, (tj | ks) != 0);
         tc::mma_commit(&stge[sb]);
       };
       tc::mbar_wait(wfull, 0);
@@ -135,20 +151,22 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         const int as = ti & 1;
         tc::mbar_wait(&acce[as], ((ti >> 1) & 1) ^ 1);
         tc::tc_fence_after();
+        const int p0 = (tile % TILES_PER_IMG) * TILE_STRIDE;
+        const int row0 = p0 - (p0 / H1) * H1;            // raster offset of lane 0 inside the box (box row 2 = ybase)
         for (int half = 0; half < 2; half++, it++) {
           const int s = it % STAGES;
           tc::mbar_wait(&full[s], (it / STAGES) & 1);
           tc::tc_fence_after();
-          const uint64_t da0 = tc::make_smem_desc(tc::smem_u32(sA + s * A_STAGE), 16, SBO_HALO, 2);
-          const uint64_t dw0 = tc::desc_advance(dW0, half * 4096);
+          const uint64_t da0 = tc::make_smem_desc(tc::smem_u32(sA + s * A_STAGE), 16, 1024, 2);
 #pragma unroll
-          for (int tap = 0; tap < 9; tap++) {
-            const int kh = tap / 3, kw = tap % 3;
-            // output (y,x) needs dY2[y-kh][x-kw] = halo row (y+2-kh)*10 + (x+2-kw)
+          for (int kh = 0; kh < 3; kh++) {
+            // output raster position p needs dY2 row (y - kh) = box raster p - p0 + row0 + (2 - kh) * 26
+            const uint64_t da = tc::desc_advance(da0, (row0 + (2 - kh) * BOX_W) * 128);
+            const uint64_t dw = tc::desc_advance(dW0, (kh * 2 + half) * 3 * 4096);
 #pragma unroll
             for (int k = 0; k < 4; k++)
-              tc::mma_tf32(tmem + as * 32, tc::desc_advance(da0, ((2 - kh) * 10 + (2 - kw)) * 128 + k * 32),
-                           tc::desc_advance(dw0, tap * 8192 + k * 32), idesc, (half | tap | k) != 0);
+              tc::mma_tf32(tmem + as * ACC_N, tc::desc_advance(da, k * 32), tc::desc_advance(dw, k * 32), idesc,
+                           (half | kh | k) != 0);
           }
           tc::mma_commit(&empty[s]);
         }
@@ -162,21 +180,64 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     }
   } else if (warp >= 4) {
     const int q = warp & 3;
-    const int r = q * 32 + lane;               // accumulator row: y = r/8, x = r%8 inside the tile
+    const int r = q * 32 + lane;               // accumulator row = raster position p0 + r
     int ti = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
       const int as = ti & 1;
       tc::mbar_wait(&accf[as], (ti >> 1) & 1);
       tc::tc_fence_after();
-      float v[32];
-      tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + as * 32, v);
+      // da1[p] = Z[p][kw=0] + Z[p-1][kw=1] + Z[p-2][kw=2]: neighbours are the lanes below (shuffles); the
+      // first two lanes of warps 1..3 take them from the previous warp through a small smem exchange
+      float v[32], t[32];
+      const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + as * ACC_N;
+      float* xw = sXch + ((ti & 1) * 4 + q) * 96;
+      tc::tmem_ld_x32(trow, v);
+      tc::tmem_ld_x32(trow + 32, t);
+      tc::tmem_ld_wait();
+      if (lane == 31) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) reinterpret_cast<float4*>(xw)[j] = make_float4(t[4 * j], t[4 * j + 1], t[4 * j + 2], t[4 * j + 3]);
+      }
+#pragma unroll
+      for (int j = 0; j < 32; j++) {
+        const float u = __shfl_up_sync(0xffffffffu, t[j], 1);
+        v[j] += lane >= 1 ? u : 0.f;
+      }
+      tc::tmem_ld_x32(trow + 64, t);
       tc::tmem_ld_wait();
       tc::tc_fence_before();
       tc::mbar_arrive(&acce[as]);
-      const int b = tile / 8, ty = (tile % 8) / TILES_X, tx = tile % TILES_X;
-      const int y = ty * TH + (r >> 3), x = tx * TW + (r & 7);
-      const bool valid = y < H1 && x < H1;
-      const long long off = (((long long)b * H1 + y) * H1 + x) * C1;
+      if (lane >= 30) {
+        float4* d = reinterpret_cast<float4*>(xw + (lane == 30 ? 32 : 64));
+#pragma unroll
+        for (int j = 0; j < 8; j++) d[j] = make_float4(t[4 * j], t[4 * j + 1], t[4 * j + 2], t[4 * j + 3]);
+      }
+#pragma unroll
+      for (int j = 0; j < 32; j++) {
+        const float u = __shfl_up_sync(0xffffffffu, t[j], 2);
+        v[j] += lane >= 2 ? u : 0.f;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");      // the four epilogue warps
+      if (q >= 1 && lane < 2) {
+        const float4* xr = reinterpret_cast<const float4*>(sXch + ((ti & 1) * 4 + q - 1) * 96);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          float4 a;
+          if (lane == 0) {
+            const float4 a1v = xr[j], a2v = xr[8 + j];
+            a = make_float4(a1v.x + a2v.x, a1v.y + a2v.y, a1v.z + a2v.z, a1v.w + a2v.w);
+          } else {
+            a = xr[16 + j];
+          }
+          v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
+        }
+      }
+      const int b = tile / TILES_PER_IMG, tt = tile % TILES_PER_IMG;
+      const int pos = tt * TILE_STRIDE + r;
+      const int y = pos / H1, x = pos - y * H1;
+      // lanes 0,1 of tiles 1..5 repeat the previous tile's last two positions: donors only
+      const bool valid = pos < NPOS && (r >= 2 || tt == 0);
+      const long long off = ((long long)b * NPOS + pos) * C1;
       if (valid) {
         const float4* act = reinterpret_cast<const float4*>(p.a1 + off);
 #pragma unroll
@@ -234,7 +295,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       tc::mbar_wait(w1done, 0);
       tc::tc_fence_after();
       float w[32];
-      tc::tmem_ld_x32(tmem + 64, w);
+      tc::tmem_ld_x32(tmem + W1_COL, w);
       tc::tmem_ld_wait();
       if (ti > 0 && lane < 10) {
         float* d = lane < 9 ? p.g_w1 + lane * 32 : p.g_b1;
@@ -370,7 +431,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
   {
     uint64_t dims[4] = {64, 24, 24, (uint64_t)B};
     uint64_t str[3] = {256, 24 * 256, 24 * 24 * 256};
-    uint32_t box[4] = {32, 10, 18, 1};
+    uint32_t box[4] = {32, dg::BOX_W, dg::BOX_H, 1};
     if (tc::make_tmap(&tmG, dy2, 4, dims, str, box)) return -2;
     uint64_t wd[2] = {64, 288};
     uint64_t ws[1] = {256};
@@ -382,7 +443,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
     if (cudaFuncSetAttribute(dg::conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dg::SMEM_BYTES) != cudaSuccess) return -10;
     attr = true;
   }
-  dg::Params p{B, B * 8, a1, da1, x, g_w1, g_b1};
+  dg::Params p{B, B * dg::TILES_PER_IMG, a1, da1, x, g_w1, g_b1};
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
   return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(256), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);
