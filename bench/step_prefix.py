@@ -14,7 +14,7 @@ import bench as B
 import horovod_distributed_example_b200 as hvd
 from horovod_distributed_example_b200 import keras
 
-ORDER = ["conv1_fwd", "fprop", "d1fwd", "head", "dx", "dw", "b0", "dgrad", "wgrad", "colsum", "b1"]
+ORDER = ["conv1_fwd", "fprop", "d1fwd", "head", "dx", "dw", "b0", "dgrad", "wgrad", "b1"]
 
 
 def main():
@@ -53,9 +53,8 @@ def main():
         rows.append({"prefix_ends_with": ORDER[k - 1], "replay_us": round(t, 2), "added_us": round(t - prev, 2)})
         prev = t
     extra = {
-        "full_without_wgrad_branch": round(measure([o for o in ORDER if o not in ("wgrad", "colsum")]), 2),
+        "full_without_wgrad": round(measure([o for o in ORDER if o != "wgrad"]), 2),
         "full_without_dgrad": round(measure([o for o in ORDER if o != "dgrad"]), 2),
-        "full_without_colsum": round(measure([o for o in ORDER if o != "colsum"]), 2),
         "full_without_b0": round(measure([o for o in ORDER if o != "b0"]), 2),
         "full_without_dw_b0": round(measure([o for o in ORDER if o not in ("b0", "dw")]), 2),
         "forward_only": round(measure(ORDER[:4]), 2),

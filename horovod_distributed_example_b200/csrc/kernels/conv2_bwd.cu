@@ -18,14 +18,14 @@
 //        ReLU mask, optional da1 store, and the staging tiles of the fused conv1 weight gradient.
 //
 // wgrad  dW2[kh,kw,ci,co] = sum_{b,oy,ox} a1[b,oy+kh,ox+kw,ci] * dY2[b,oy,ox,co]
-//        the reduction runs over pixels, so BOTH operands are MN-major: A[(tap,ci)][pixel] and
-//        B[co][pixel] are the activation tensors themselves ([pixel][channel] rows).  One haloed a1
-//        tile (10x10 pixels) per patch serves all 9 taps: per kernel row kh the M atoms are the kw
-//        shifts of the same rows (LBO = one row = 128 B, i.e. overlapping atoms).  Three accumulators
-//        in TMEM (kh = 0,1,2).  The bias gradient is a plain column sum of dY2 (hvd_colsum64) that
-//        runs on another branch of the step's DAG, off the critical path.
-//        Each CTA reduces a slice of the pixels (split-K over 8x8 patches) and adds its 288x64 result
-//        into the arena with red.add.v4.
+//        the reduction runs over pixels, so BOTH operands are MN-major: A[(kw,ci)][pixel] and
+//        B[(kh,co)][pixel] are the activation tensors themselves ([pixel][channel] rows).  The M atoms are
+//        the kw shifts of one a1 row (LBO = one row = 128 B, i.e. overlapping atoms) and the N atoms are
+//        the three dY2 rows that pair with it, both channel halves (N = 192): one MMA per a1 row does all
+//        nine taps.  The bias gradient (column sums of dY2) is summed from the smem tile by the otherwise
+//        idle epilogue warps while the tensor core works.  Details at namespace wg.
+//        Each CTA reduces a range of 8-column image strips (split-K) and adds its 288x64 result into the
+//        arena with red.add.v4.
 #include "mnist_common.cuh"
 #include "tc_common.cuh"
 
@@ -312,18 +312,29 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
 
 // ============================================================================ wgrad
 namespace wg {
-constexpr int HALO_BYTES = 13 * 1024;       // box {32 ci, 10 w, 10 h, 1 n} = 100 rows x 128 B (12,800 B)
-constexpr int HALO_TX = 100 * 128;
-constexpr int DY_SLOT = 8192;               // box {32 co, 8 w, 8 h, 1 n}
-constexpr int STAGE = HALO_BYTES + 2 * DY_SLOT + 1024;   // + slack so the dummy 4th atom stays in bounds
-constexpr int STAGE_TX = HALO_TX + 2 * DY_SLOT;
-constexpr int STAGES = 4;
-constexpr int ONES_BYTES = 1024;            // spare 1 KB between the stages and the barriers
-constexpr int SMEM_BYTES = STAGES * STAGE + ONES_BYTES + 1024 + 256;
-constexpr int TMEM_COLS = 256;              // kh = 0,1,2 accumulators, 64 columns each (power-of-two allocation)
+// One work item = an 8-column strip of one image over its full height:
+//   A: a1 halo box {32 ci, 10 w, 26 h}            -> raster [h][w], row (h, w) at (h*10 + w) * 128 B
+//   B: dY2 box {32 co, 8 w, 2 halves, 28 h} from a 5-D view of dY2 whose third dimension is the channel
+//      half (stride 128 B) -> raster [h][half][w]: the 8 pixels of (row h, half) are one contiguous 1 KB
+//      K-slab at ((h*2 + half) * 8) * 128 B.  Rows -2,-1 and 24,25 are TMA zero fill.
+// One MMA per a1 row hr (K = its 8 pixels): M atoms = the kw shifts of that row (LBO = one row, the 4th atom
+// is a dummy), N atoms = (kh', half) for the dY2 rows hr-2+kh' (LBO = 1 KB):
+//   D[(kw,ci)][(kh',half,co)] += a1[hr][x+kw][ci] * dY2[hr-2+kh'][x][co]      kh = 2 - kh'
+// 26 MMAs of N = 192 (~97 cycles each) per strip, where one MMA per (row, kh) of N = 64 cost 3 x 77.
+constexpr int HALO_ROWS = 26 * 10;
+constexpr int HALO_TX = HALO_ROWS * 128;    // 33,280 B
+constexpr int HALO_BYTES = 33 * 1024;       // + 4 slack rows: the dummy 4th atom of the last row reads one row past the box
+constexpr int DY_ROWS = 28 * 2 * 8;
+constexpr int DY_BYTES = DY_ROWS * 128;     // 57,344 B
+constexpr int STAGE = HALO_BYTES + DY_BYTES;
+constexpr int STAGE_TX = HALO_TX + DY_BYTES;
+constexpr int STAGES = 2;
+constexpr int SMEM_BYTES = STAGES * STAGE + 1024 /*base align*/ + 1024 /*barriers*/ + 256;
+constexpr int ACC_N = 192;
+constexpr int TMEM_COLS = 256;
 
 struct Params {
-  int B, n_patches, patches_per_cta;
+  int B, n_strips, strips_per_cta;
   float* g_w;                               // [288][64]
   float* g_b;                               // [64]
 };
@@ -332,26 +343,26 @@ __global__ void __launch_bounds__(256, 1)
 conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmG, Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sOnes = smem + STAGES * STAGE;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sOnes + ONES_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE);
   uint64_t* full = bars;
   uint64_t* empty = bars + STAGES;
   uint64_t* accf = bars + 2 * STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accf + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int p_begin = blockIdx.x * p.patches_per_cta;
-  const int p_end = min(p.n_patches, p_begin + p.patches_per_cta);
-  const int np = p_end - p_begin;
+  const int s_begin = blockIdx.x * p.strips_per_cta;
+  const int s_end = min(p.n_strips, s_begin + p.strips_per_cta);
+  const int ns = s_end - s_begin;
   if (warp == 0 && lane == 0) { tc::tma_prefetch_desc(&tmA); tc::tma_prefetch_desc(&tmG); }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < STAGES; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 1); }
+    // a stage is free again when the tensor core (1 commit) and the four bias-sum warps (1 arrive each) are done
+    for (int s = 0; s < STAGES; s++) { tc::mbar_init(&full[s], 1); tc::mbar_init(&empty[s], 5); }
     tc::mbar_init(accf, 1);
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
   // the slack rows after each halo tile are read by the dummy 4th atom: keep them finite
-  for (int i = threadIdx.x; i < STAGES * 128; i += blockDim.x)       // rows 100..103 of each halo slot
+  for (int i = threadIdx.x; i < STAGES * 4 * 32; i += blockDim.x)
     reinterpret_cast<float*>(smem + (i / 128) * STAGE + HALO_TX)[i % 128] = 0.f;
   tc::fence_proxy_async();
   tc::tc_fence_before();
@@ -363,53 +374,71 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
   if (warp == 0) {
     if (tc::elect_one()) {
-      for (int i = 0; i < np; i++) {
+      for (int i = 0; i < ns; i++) {
         const int s = i % STAGES;
         tc::mbar_wait(&empty[s], ((i / STAGES) & 1) ^ 1);
         tc::mbar_expect_tx(&full[s], STAGE_TX);
-        const int patch = p_begin + i;
-        const int b = patch / 9, py = (patch % 9) / 3, px = patch % 3;
+        const int strip = s_begin + i;
+        const int b = strip / 3, px = strip % 3;
         uint8_t* st = smem + s * STAGE;
-        tc::tma_load_4d(st, &tmA, &full[s], 0, px * 8, py * 8, b);                       // a1 halo, once
-        tc::tma_load_4d(st + HALO_BYTES, &tmG, &full[s], 0, px * 8, py * 8, b);           // dY2 co 0..31
-        tc::tma_load_4d(st + HALO_BYTES + DY_SLOT, &tmG, &full[s], 32, px * 8, py * 8, b);  // dY2 co 32..63
+        tc::tma_load_4d(st, &tmA, &full[s], 0, px * 8, 0, b);                      // a1 columns px*8 .. px*8+9, all 26 rows
+        tc::tma_load_5d(st + HALO_BYTES, &tmG, &full[s], 0, px * 8, 0, -2, b);     // dY2 rows -2..25, both halves
       }
     }
   } else if (warp == 1) {
     if (tc::elect_one()) {
-      constexpr uint32_t idesc = tc::make_idesc_tf32(128, 64, 1, 1);
-      for (int i = 0; i < np; i++) {
+      constexpr uint32_t idesc = tc::make_idesc_tf32(128, ACC_N, 1, 1);
+      for (int i = 0; i < ns; i++) {
         const int s = i % STAGES;
         tc::mbar_wait(&full[s], (i / STAGES) & 1);
         tc::tc_fence_after();
         const uint32_t halo = tc::smem_u32(smem + s * STAGE);
-        const uint32_t dy = halo + HALO_BYTES;
         const uint64_t da0 = tc::make_smem_desc(halo, 128, 512, 1);
-        const uint64_t db0 = tc::desc_mnmajor(dy, DY_SLOT);
-#pragma unroll
-        for (int ks = 0; ks < 8; ks++) {       // output row ks of the patch = 8 pixels = one K=8 MMA step
-#pragma unroll
-          for (int kh = 0; kh < 3; kh++)       // M atoms = kw 0,1,2 (+1 dummy): the SAME halo rows shifted by one row each
-            tc::mma_tf32(tmem + kh * 64, tc::desc_advance(da0, (ks + kh) * 10 * 128), tc::desc_advance(db0, ks * 1024),
-                         idesc, (i | ks) != 0);
-        }
+        const uint64_t db0 = tc::make_smem_desc(halo + HALO_BYTES, 1024, 512, 1);
+#pragma unroll 2
+        for (int hr = 0; hr < 26; hr++)
+          tc::mma_tf32(tmem, tc::desc_advance(da0, hr * 1280), tc::desc_advance(db0, hr * 2048), idesc, (i | hr) != 0);
         tc::mma_commit(&empty[s]);
       }
       tc::mma_commit(accf);
     }
-  } else if (warp >= 4 && np > 0) {
+  } else if (warp >= 4 && ns > 0) {
+    // ---- while the tensor core works: conv2's bias gradient = column sums of the dY2 tile (every dY2 pixel
+    // is in exactly one strip; the halo rows are zeros).  Thread t reads the 16-byte chunk at position t%8 of
+    // rows t/8, t/8+16, ...: r & 3 and the channel half (r >> 3) & 1 are the same for all of them, so after
+    // undoing the 32-byte-atom swizzle each thread owns four fixed channels.
     const int q = warp & 3;
-    tc::mbar_wait(accf, 0);                   // accumulator row: kw = q, ci = lane
+    const int t = threadIdx.x - 128;
+    const int pc = t & 7, rbase = t >> 3;
+    float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < ns; i++) {
+      const int s = i % STAGES;
+      tc::mbar_wait(&full[s], (i / STAGES) & 1);
+      const uint8_t* dy = smem + s * STAGE + HALO_BYTES;
+#pragma unroll 4
+      for (int k = 0; k < DY_ROWS / 16; k++) {
+        const float4 v = *reinterpret_cast<const float4*>(dy + (rbase + 16 * k) * 128 + pc * 16);
+        bs.x += v.x; bs.y += v.y; bs.z += v.z; bs.w += v.w;
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&empty[s]);
+    }
+    {
+      const int half = (rbase >> 3) & 1;
+      const int c32 = (pc >> 1) ^ (rbase & 3);
+      tc::red_add_f4(p.g_b + half * 32 + c32 * 8 + (pc & 1) * 4, bs.x, bs.y, bs.z, bs.w);
+    }
+    // ---- epilogue: accumulator row = (kw = q, ci = lane); column block a = kh'*2 + half
+    tc::mbar_wait(accf, 0);
     tc::tc_fence_after();
+    if (q != 3) {                             // the 4th M atom is the dummy shift (warp-uniform skip)
 #pragma unroll 1
-    for (int g = 0; g < 3; g++) {
-      if (q == 3) continue;                   // 4th atom of a kh accumulator is the dummy shift
-#pragma unroll 1
-      for (int c = 0; c < 64; c += 32) {
+      for (int a = 0; a < 6; a++) {
         float v[32];
-        tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + g * 64 + c, v);
+        tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + a * 32, v);
         tc::tmem_ld_wait();
-        float* d = p.g_w + ((long long)(g * 3 + q) * 32 + lane) * 64 + c;
+        const int kh = 2 - (a >> 1);
+        float* d = p.g_w + ((long long)((kh * 3 + q) * 32 + lane)) * 64 + (a & 1) * 32;
 #pragma unroll
         for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
       }
@@ -449,19 +478,20 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
   return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(256), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);
 }
 
-// g_w is ACCUMULATED into (red.add): the caller zeroes it before the step.  g_b is not written here any
-// more (kept in the signature for ABI stability): use hvd_colsum64(dy2, g_b, B*576).
+// g_w [3][3][32][64] and g_b [64] are ACCUMULATED into (red.add): the caller zeroes them before the step.
 extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream) {
   CUtensorMap tmA, tmG;
   {
     uint64_t dims[4] = {32, 26, 26, (uint64_t)B};
     uint64_t str[3] = {128, 26 * 128, 26 * 26 * 128};
-    uint32_t hbox[4] = {32, 10, 10, 1};
+    uint32_t hbox[4] = {32, 10, 26, 1};
     if (tc::make_tmap(&tmA, a1, 4, dims, str, hbox, true)) return -2;
-    uint64_t gd[4] = {64, 24, 24, (uint64_t)B};
-    uint64_t gs[3] = {256, 24 * 256, 24 * 24 * 256};
-    uint32_t box[4] = {32, 8, 8, 1};
-    if (tc::make_tmap(&tmG, dy2, 4, gd, gs, box, true)) return -3;
+    // dY2 [B][24][24][64] seen as {32 co, 24 w, 2 halves, 24 h, B}: the channel half is its own dimension so
+    // one box lands in smem as [h][half][w]
+    uint64_t gd[5] = {32, 24, 2, 24, (uint64_t)B};
+    uint64_t gs[4] = {256, 128, 24 * 256, 24 * 24 * 256};
+    uint32_t box[5] = {32, 8, 2, 28, 1};
+    if (tc::make_tmap(&tmG, dy2, 5, gd, gs, box, true)) return -3;
   }
   static bool attr = false;
   if (!attr) {
@@ -469,10 +499,11 @@ extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, fl
     attr = true;
   }
   wg::Params p;
-  p.B = B; p.n_patches = B * 9;
-  if (ctas <= 0) ctas = 144;
-  p.patches_per_cta = (p.n_patches + ctas - 1) / ctas;
-  ctas = (p.n_patches + p.patches_per_cta - 1) / p.patches_per_cta;
+  p.B = B; p.n_strips = B * 3;
+  if (ctas <= 0) ctas = 128;
+  if (ctas > p.n_strips) ctas = p.n_strips;
+  p.strips_per_cta = (p.n_strips + ctas - 1) / ctas;
+  ctas = (p.n_strips + p.strips_per_cta - 1) / p.strips_per_cta;
   p.g_w = g_w; p.g_b = g_b;
   return (int)tc::launch_pdl(wg::conv2_wgrad_kernel, dim3(ctas), dim3(256), wg::SMEM_BYTES, (cudaStream_t)stream, tmA, tmG, p);
 }

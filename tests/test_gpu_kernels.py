@@ -198,9 +198,16 @@ def test_conv2_dgrad_and_wgrad_and_conv1_wgrad():
     gb = torch.zeros(64, device="cuda")
     assert lib.hvd_conv2_wgrad(a1r.data_ptr(), dy2.data_ptr(), gw.data_ptr(), gb.data_ptr(), B, 0, _s()) == 0
     assert _rel(gw, dw_ref) < 3e-3
+    assert _rel(gb, dy2.double().sum(dim=(0, 1, 2))) < 1e-4          # bias gradient summed inside the wgrad kernel
+    for ctas in (48, 148, 7):                                        # uneven strip ranges, accumulate semantics
+        gw2 = torch.ones(3, 3, 32, 64, device="cuda")
+        gb2 = torch.ones(64, device="cuda")
+        assert lib.hvd_conv2_wgrad(a1r.data_ptr(), dy2.data_ptr(), gw2.data_ptr(), gb2.data_ptr(), B, ctas, _s()) == 0
+        assert _rel(gw2 - 1.0, dw_ref) < 3e-3 and _rel(gb2 - 1.0, dy2.double().sum(dim=(0, 1, 2))) < 1e-3
+    gb3 = torch.zeros(64, device="cuda")
     lib.hvd_colsum64.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p]
-    assert lib.hvd_colsum64(dy2.data_ptr(), gb.data_ptr(), B * 576, _s()) == 0
-    assert _rel(gb, dy2.double().sum(dim=(0, 1, 2))) < 1e-4
+    assert lib.hvd_colsum64(dy2.data_ptr(), gb3.data_ptr(), B * 576, _s()) == 0
+    assert _rel(gb3, dy2.double().sum(dim=(0, 1, 2))) < 1e-4
     # conv1 wgrad (CUDA cores)
     g1w = torch.zeros(3, 3, 1, 32, device="cuda")
     g1b = torch.zeros(32, device="cuda")
