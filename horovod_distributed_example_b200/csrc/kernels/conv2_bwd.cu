@@ -40,7 +40,7 @@ constexpr int A_STAGE = BOX_W * BOX_H * 128;   // 208 rows x 128 B = 26,624 B (a
 constexpr int A_TX = A_STAGE;
 constexpr int W_BYTES = 18 * 4096;
 constexpr int STG_BYTES = 32 * 1024;        // fused conv1-wgrad staging: im2col(x) tile 16 KB + da1 tile 16 KB
-constexpr int XCH_BYTES = 2 * 4 * 96 * 4;   // kw-reduction exchange across warp boundaries, double-buffered
+constexpr int XCH_BYTES = 2 * 2 * 4 * 96 * 4;   // kw-reduction exchange across warp boundaries: 2 warp sets, double-buffered
 constexpr int SMEM_BYTES = W_BYTES + STAGES * A_STAGE + 2 * STG_BYTES + XCH_BYTES + 1024 /*base align*/ + 1024 /*barriers*/ + 256;
 constexpr int TMEM_COLS = 256;              // 2 dgrad stages x 96 columns + 32 columns for the conv1 wgrad accumulator
 constexpr int ACC_N = 96;                   // (kw, ci)
@@ -64,7 +64,7 @@ __device__ __forceinline__ float* stg_chunk(uint8_t* tile, int r, int c) {
   return reinterpret_cast<float*>(tile + r * 128 + ((c ^ (r & 3)) << 5));
 }
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(384, 1)
 conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmW, Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -171,18 +171,24 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           tc::mma_commit(&empty[s]);
         }
         tc::mma_commit(&accf[as]);
-        if (fuse_w1 && ti > 0) w1_mma(ti - 1);          // conv1 wgrad of the PREVIOUS tile (its epilogue ran meanwhile)
+        // conv1 wgrad of the tile TWO back: its epilogue (the other tile of the same warp set) has finished
+        // staging by the time this tile's main MMAs are queued, so the issue thread never waits here long
+        if (fuse_w1 && ti > 1) w1_mma(ti - 2);
       }
       if (fuse_w1) {
-        if (ti > 0) w1_mma(ti - 1);
+        for (int tj = ti > 2 ? ti - 2 : 0; tj < ti; tj++) w1_mma(tj);
         tc::mma_commit(w1done);
       }
     }
   } else if (warp >= 4) {
+    // Two epilogue warp sets (warps 4-7 and 8-11) alternate tiles: set s owns accumulator stage s, staging
+    // buffer s and its own exchange buffers, so one tile's long-latency epilogue (TMEM loads, a1 / x loads
+    // from L2, staging stores) overlaps the other's.
     const int q = warp & 3;
+    const int set = (warp - 4) >> 2;
     const int r = q * 32 + lane;               // accumulator row = raster position p0 + r
-    int ti = 0;
-    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
+    int ti = set;
+    for (int tile = blockIdx.x + set * gridDim.x; tile < p.n_tiles; tile += 2 * gridDim.x, ti += 2) {
       const int as = ti & 1;
       tc::mbar_wait(&accf[as], (ti >> 1) & 1);
       tc::tc_fence_after();
@@ -190,7 +196,8 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       // first two lanes of warps 1..3 take them from the previous warp through a small smem exchange
       float v[32], t[32];
       const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + as * ACC_N;
-      float* xw = sXch + ((ti & 1) * 4 + q) * 96;
+      const int xb = set * 2 + ((ti >> 1) & 1);
+      float* xw = sXch + (xb * 4 + q) * 96;
       tc::tmem_ld_x32(trow, v);
       tc::tmem_ld_x32(trow + 32, t);
       tc::tmem_ld_wait();
@@ -217,9 +224,10 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         const float u = __shfl_up_sync(0xffffffffu, t[j], 2);
         v[j] += lane >= 2 ? u : 0.f;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");      // the four epilogue warps
+      if (set == 0) asm volatile("bar.sync 1, 128;" ::: "memory");      // the four warps of this set
+      else          asm volatile("bar.sync 2, 128;" ::: "memory");
       if (q >= 1 && lane < 2) {
-        const float4* xr = reinterpret_cast<const float4*>(sXch + ((ti & 1) * 4 + q - 1) * 96);
+        const float4* xr = reinterpret_cast<const float4*>(sXch + (xb * 4 + q - 1) * 96);
 #pragma unroll
         for (int j = 0; j < 8; j++) {
           float4 a;
@@ -290,8 +298,9 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         tc::mbar_arrive(&stgf[sb]);
       }
     }
-    if (fuse_w1 && q == 0) {
+    if (fuse_w1 && warp == 4) {
       // rows 0..8 of the conv1-wgrad accumulator are the 9 taps, row 9 is the bias gradient
+      ti = blockIdx.x < p.n_tiles ? 1 : 0;
       tc::mbar_wait(w1done, 0);
       tc::tc_fence_after();
       float w[32];
@@ -475,7 +484,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
   dg::Params p{B, B * dg::TILES_PER_IMG, a1, da1, x, g_w1, g_b1};
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
-  return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(256), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);
+  return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(384), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);
 }
 
 // g_w [3][3][32][64] and g_b [64] are ACCUMULATED into (red.add): the caller zeroes them before the step.

@@ -49,6 +49,10 @@ def reload():
 def default_ctas(nbytes: int, variant: int, nranks: int) -> int:
     """Enough CTAs to keep ~2 MB in flight on NVLink for large messages, one for tiny ones."""
     work = nbytes if variant == ONESHOT else max(nbytes // max(nranks, 1), 1)
+    if nranks <= 1:
+        # single GPU: the "allreduce" is just the fused optimizer update - a pure streaming kernel that wants two
+        # CTAs per SM (measured: 4.7 MB bucket 18 us at 148 CTAs, 11 us at 296)
+        return int(max(1, min(296, (work + 16383) // 16384)))
     cap = 32 if variant == NVLS else 148   # measured: multimem traffic peaks around 32 CTAs (profiles/allreduce_sweep_N8.json)
     return int(max(1, min(cap, (work + 16383) // 16384)))      # <= one CTA per SM: always co-resident
 

@@ -194,6 +194,14 @@ def test_conv2_dgrad_and_wgrad_and_conv1_wgrad():
     assert lib.hvd_conv2_dgrad(dy2.data_ptr(), w2.data_ptr(), a1r.data_ptr(), da1.data_ptr(), B, 0, _s(),
                                x.data_ptr(), f1w.data_ptr(), f1b.data_ptr()) == 0
     assert _rel(da1, da_ref) < 3e-3
+    for ctas in (5, 3):            # many tiles per CTA: both epilogue warp sets, staging/TMEM stage reuse, odd tails
+        da1b = torch.full_like(a1, 5.0)
+        f1w2 = torch.zeros(3, 3, 1, 32, device="cuda")
+        f1b2 = torch.zeros(32, device="cuda")
+        assert lib.hvd_conv2_dgrad(dy2.data_ptr(), w2.data_ptr(), a1r.data_ptr(), da1b.data_ptr(), B, ctas, _s(),
+                                   x.data_ptr(), f1w2.data_ptr(), f1b2.data_ptr()) == 0
+        assert _rel(da1b, da_ref) < 3e-3
+        assert _rel(f1w2, f1w) < 1e-3 and _rel(f1b2, f1b) < 1e-3
     gw = torch.zeros(3, 3, 32, 64, device="cuda")
     gb = torch.zeros(64, device="cuda")
     assert lib.hvd_conv2_wgrad(a1r.data_ptr(), dy2.data_ptr(), gw.data_ptr(), gb.data_ptr(), B, 0, _s()) == 0
