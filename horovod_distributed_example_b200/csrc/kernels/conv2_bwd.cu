@@ -32,6 +32,11 @@
 namespace {
 using namespace mnist;
 
+// Phase timers of CTA 0 (clock64 deltas, one tile in the middle of its range): a handful of clock reads by
+// three threads of one CTA, read back with hvd_conv2_bwd_debug_read() by bench/conv_bwd_timing.py.
+__device__ long long g_bwd_dbg[64];
+#define HVD_DBG_T(slot) do { if (dbg_on) g_bwd_dbg[slot] = clock64(); } while (0)
+
 // ============================================================================ dgrad
 namespace dg {
 constexpr int STAGES = 3;
@@ -149,14 +154,18 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       int it = 0, ti = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
         const int as = ti & 1;
+        const bool dbg_on = blockIdx.x == 0 && (ti == 2 || ti == 3);
+        HVD_DBG_T(8 + (ti & 1) * 8);
         tc::mbar_wait(&acce[as], ((ti >> 1) & 1) ^ 1);
         tc::tc_fence_after();
+        HVD_DBG_T(9 + (ti & 1) * 8);
         const int p0 = (tile % TILES_PER_IMG) * TILE_STRIDE;
         const int row0 = p0 - (p0 / H1) * H1;            // raster offset of lane 0 inside the box (box row 2 = ybase)
         for (int half = 0; half < 2; half++, it++) {
           const int s = it % STAGES;
           tc::mbar_wait(&full[s], (it / STAGES) & 1);
           tc::tc_fence_after();
+          HVD_DBG_T(12 + (ti & 1) * 8 + half);
           const uint64_t da0 = tc::make_smem_desc(tc::smem_u32(sA + s * A_STAGE), 16, 1024, 2);
 #pragma unroll
           for (int kh = 0; kh < 3; kh++) {
@@ -171,9 +180,11 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           tc::mma_commit(&empty[s]);
         }
         tc::mma_commit(&accf[as]);
+        HVD_DBG_T(10 + (ti & 1) * 8);
         // conv1 wgrad of the tile TWO back: its epilogue (the other tile of the same warp set) has finished
         // staging by the time this tile's main MMAs are queued, so the issue thread never waits here long
         if (fuse_w1 && ti > 1) w1_mma(ti - 2);
+        HVD_DBG_T(11 + (ti & 1) * 8);
       }
       if (fuse_w1) {
         for (int tj = ti > 2 ? ti - 2 : 0; tj < ti; tj++) w1_mma(tj);
@@ -190,40 +201,74 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     int ti = set;
     for (int tile = blockIdx.x + set * gridDim.x; tile < p.n_tiles; tile += 2 * gridDim.x, ti += 2) {
       const int as = ti & 1;
-      tc::mbar_wait(&accf[as], (ti >> 1) & 1);
-      tc::tc_fence_after();
+      const bool dbg_on = blockIdx.x == 0 && threadIdx.x == 128 && ti == 2;
+      const int b = tile / TILES_PER_IMG, tt = tile % TILES_PER_IMG;
+      const int pos = tt * TILE_STRIDE + r;
+      const int y = pos / H1, x = pos - y * H1;
+      // lanes 0,1 of tiles 1..5 repeat the previous tile's last two positions: donors only
+      const bool valid = pos < NPOS && (r >= 2 || tt == 0);
+      const long long off = ((long long)b * NPOS + pos) * C1;
+      // Everything this tile needs from L2 is requested BEFORE waiting for the accumulator: conv1's
+      // activations (reduced to a 32-bit ReLU mask as soon as they land) and the 3x3 input patch of the
+      // fused conv1 weight gradient.
+      uint32_t relu = 0;
+      float xin[10];
+#pragma unroll
+      for (int k = 0; k < 10; k++) xin[k] = 0.f;
+      {
+        float4 act[8];
+        if (valid) {
+          const float4* ap = reinterpret_cast<const float4*>(p.a1 + off);
+#pragma unroll
+          for (int j = 0; j < 8; j++) act[j] = __ldg(ap + j);
+          if (fuse_w1) {
+            const float* xi = p.x + ((long long)b * IMG + y) * IMG + x;
+#pragma unroll
+            for (int kh = 0; kh < 3; kh++)
+#pragma unroll
+              for (int kw = 0; kw < 3; kw++) xin[kh * 3 + kw] = __ldg(xi + kh * IMG + kw);
+            xin[9] = 1.0f;                                  // the bias "tap"
+          }
+        }
+        HVD_DBG_T(0);
+        tc::mbar_wait(&accf[as], (ti >> 1) & 1);
+        tc::tc_fence_after();
+        HVD_DBG_T(1);
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 8; j++)
+            relu |= ((act[j].x > 0.f ? 1u : 0u) | (act[j].y > 0.f ? 2u : 0u) | (act[j].z > 0.f ? 4u : 0u) | (act[j].w > 0.f ? 8u : 0u)) << (4 * j);
+        }
+      }
       // da1[p] = Z[p][kw=0] + Z[p-1][kw=1] + Z[p-2][kw=2]: neighbours are the lanes below (shuffles); the
       // first two lanes of warps 1..3 take them from the previous warp through a small smem exchange
-      float v[32], t[32];
+      float v[32], t1[32], t2[32];
       const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16) + as * ACC_N;
       const int xb = set * 2 + ((ti >> 1) & 1);
       float* xw = sXch + (xb * 4 + q) * 96;
       tc::tmem_ld_x32(trow, v);
-      tc::tmem_ld_x32(trow + 32, t);
+      tc::tmem_ld_x32(trow + 32, t1);
+      tc::tmem_ld_x32(trow + 64, t2);
       tc::tmem_ld_wait();
-      if (lane == 31) {
-#pragma unroll
-        for (int j = 0; j < 8; j++) reinterpret_cast<float4*>(xw)[j] = make_float4(t[4 * j], t[4 * j + 1], t[4 * j + 2], t[4 * j + 3]);
-      }
-#pragma unroll
-      for (int j = 0; j < 32; j++) {
-        const float u = __shfl_up_sync(0xffffffffu, t[j], 1);
-        v[j] += lane >= 1 ? u : 0.f;
-      }
-      tc::tmem_ld_x32(trow + 64, t);
-      tc::tmem_ld_wait();
+      HVD_DBG_T(6);
       tc::tc_fence_before();
-      tc::mbar_arrive(&acce[as]);
+      tc::mbar_arrive(&acce[as]);                           // the accumulator stage is free for tile ti+2
       if (lane >= 30) {
         float4* d = reinterpret_cast<float4*>(xw + (lane == 30 ? 32 : 64));
 #pragma unroll
-        for (int j = 0; j < 8; j++) d[j] = make_float4(t[4 * j], t[4 * j + 1], t[4 * j + 2], t[4 * j + 3]);
+        for (int j = 0; j < 8; j++) d[j] = make_float4(t2[4 * j], t2[4 * j + 1], t2[4 * j + 2], t2[4 * j + 3]);
+        if (lane == 31) {
+#pragma unroll
+          for (int j = 0; j < 8; j++) reinterpret_cast<float4*>(xw)[j] = make_float4(t1[4 * j], t1[4 * j + 1], t1[4 * j + 2], t1[4 * j + 3]);
+        }
       }
 #pragma unroll
       for (int j = 0; j < 32; j++) {
-        const float u = __shfl_up_sync(0xffffffffu, t[j], 2);
-        v[j] += lane >= 2 ? u : 0.f;
+        const float u1 = __shfl_up_sync(0xffffffffu, t1[j], 1);
+        const float u2 = __shfl_up_sync(0xffffffffu, t2[j], 2);
+        v[j] += (lane >= 1 ? u1 : 0.f) + (lane >= 2 ? u2 : 0.f);
       }
+      HVD_DBG_T(7);
       if (set == 0) asm volatile("bar.sync 1, 128;" ::: "memory");      // the four warps of this set
       else          asm volatile("bar.sync 2, 128;" ::: "memory");
       if (q >= 1 && lane < 2) {
@@ -240,42 +285,21 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
         }
       }
-      const int b = tile / TILES_PER_IMG, tt = tile % TILES_PER_IMG;
-      const int pos = tt * TILE_STRIDE + r;
-      const int y = pos / H1, x = pos - y * H1;
-      // lanes 0,1 of tiles 1..5 repeat the previous tile's last two positions: donors only
-      const bool valid = pos < NPOS && (r >= 2 || tt == 0);
-      const long long off = ((long long)b * NPOS + pos) * C1;
-      if (valid) {
-        const float4* act = reinterpret_cast<const float4*>(p.a1 + off);
+      HVD_DBG_T(2);
 #pragma unroll
-        for (int j = 0; j < 8; j++) {                    // conv1's ReLU backward
-          const float4 a = __ldg(act + j);
-          v[4 * j] = a.x > 0.f ? v[4 * j] : 0.f;         v[4 * j + 1] = a.y > 0.f ? v[4 * j + 1] : 0.f;
-          v[4 * j + 2] = a.z > 0.f ? v[4 * j + 2] : 0.f; v[4 * j + 3] = a.w > 0.f ? v[4 * j + 3] : 0.f;
-        }
-        if (p.da1) {
-          float4* dst = reinterpret_cast<float4*>(p.da1 + off);
+      for (int j = 0; j < 32; j++) v[j] = ((relu >> j) & 1u) ? v[j] : 0.f;     // conv1's ReLU backward (0 for invalid lanes)
+      if (valid && p.da1) {
+        float4* dst = reinterpret_cast<float4*>(p.da1 + off);
 #pragma unroll
-          for (int j = 0; j < 8; j++) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        }
+        for (int j = 0; j < 8; j++) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
       }
+      HVD_DBG_T(3);
       if (fuse_w1) {
         const int sb = ti & 1;
         tc::mbar_wait(&stge[sb], ((ti >> 1) & 1) ^ 1);    // the tensor core is done with this staging tile
+        HVD_DBG_T(4);
         uint8_t* tA = sStg + sb * STG_BYTES;
         uint8_t* tB = tA + 16384;
-        float xin[12];
-#pragma unroll
-        for (int k = 0; k < 12; k++) xin[k] = 0.f;
-        if (valid) {
-          const float* xi = p.x + ((long long)b * IMG + y) * IMG + x;
-#pragma unroll
-          for (int kh = 0; kh < 3; kh++)
-#pragma unroll
-            for (int kw = 0; kw < 3; kw++) xin[kh * 3 + kw] = __ldg(xi + kh * IMG + kw);
-          xin[9] = 1.0f;                                  // the bias "tap"
-        }
         float4* a0 = reinterpret_cast<float4*>(stg_chunk(tA, r, 0));
         a0[0] = make_float4(xin[0], xin[1], xin[2], xin[3]);
         a0[1] = make_float4(xin[4], xin[5], xin[6], xin[7]);
@@ -291,22 +315,22 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
 #pragma unroll
         for (int c = 0; c < 4; c++) {
           float4* d = reinterpret_cast<float4*>(stg_chunk(tB, r, c));
-          d[0] = valid ? make_float4(v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]) : make_float4(0.f, 0.f, 0.f, 0.f);
-          d[1] = valid ? make_float4(v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]) : make_float4(0.f, 0.f, 0.f, 0.f);
+          d[0] = make_float4(v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]);      // masked: 0 on invalid lanes
+          d[1] = make_float4(v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]);
         }
         tc::fence_proxy_async();                          // generic-proxy smem writes -> visible to the tensor core
         tc::mbar_arrive(&stgf[sb]);
       }
+      HVD_DBG_T(5);
     }
     if (fuse_w1 && warp == 4) {
       // rows 0..8 of the conv1-wgrad accumulator are the 9 taps, row 9 is the bias gradient
-      ti = blockIdx.x < p.n_tiles ? 1 : 0;
       tc::mbar_wait(w1done, 0);
       tc::tc_fence_after();
       float w[32];
       tc::tmem_ld_x32(tmem + W1_COL, w);
       tc::tmem_ld_wait();
-      if (ti > 0 && lane < 10) {
+      if (blockIdx.x < p.n_tiles && lane < 10) {
         float* d = lane < 9 ? p.g_w1 + lane * 32 : p.g_b1;
 #pragma unroll
         for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, w[j], w[j + 1], w[j + 2], w[j + 3]);
@@ -442,7 +466,10 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc::tc_fence_after();
     if (q != 3) {                             // the 4th M atom is the dummy shift (warp-uniform skip)
 #pragma unroll 1
-      for (int a = 0; a < 6; a++) {
+      for (int a6 = 0; a6 < 6; a6++) {
+        // every CTA adds into the same 288x64 block: start each one at a different column block so the
+        // red.adds of CTAs that finish together land on different addresses
+        const int a = (a6 + blockIdx.x) % 6;
         float v[32];
         tc::tmem_ld_x32(tmem + ((uint32_t)(q * 32) << 16) + a * 32, v);
         tc::tmem_ld_wait();
@@ -488,6 +515,10 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
 }
 
 // g_w [3][3][32][64] and g_b [64] are ACCUMULATED into (red.add): the caller zeroes them before the step.
+extern "C" int hvd_conv2_bwd_debug_read(long long* out64) {
+  return (int)cudaMemcpyFromSymbol(out64, g_bwd_dbg, sizeof(long long) * 64);
+}
+
 extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream) {
   CUtensorMap tmA, tmG;
   {
