@@ -1,0 +1,492 @@
+"""The fused MNIST-CNN engine: the reference's flagship model (``mnist_keras.py:71-81``,
+``tensorflow2_keras_mnist.py:43-52``) as a CUDA-graph-captured chain of hand-written sm_100a
+kernels.  Selected automatically by ``Model.compile`` when the layer stack matches.
+
+One training step = 11 launches replayed from a CUDA graph (no Python per layer, no host sync):
+
+    conv1_fwd (CUDA cores, K=9)                          csrc/kernels/mnist_small.cu
+    conv2_fprop   tcgen05 implicit GEMM + bias/ReLU/maxpool/dropout epilogue   conv2_fprop.cu
+    dense1 fwd    tcgen05 split-K GEMM (x[B,9216] * W[9216,128])              tc_gemm.cu
+    head          bias/ReLU/dropout, Dense(10)+softmax+CE+accuracy, dense2 backward, dense1 mask bwd
+    dense1 dX     tcgen05 GEMM + maxpool/dropout/ReLU-backward scatter epilogue (EPI_UNPOOL)
+    dense1 dW     tcgen05 GEMM (both operands MN-major) -> written straight into the grad arena
+       -> bucket 0 (98% of the bytes) starts its fused allreduce+update on a side stream here
+    conv2_dgrad   tcgen05 implicit GEMM, zero padding by TMA OOB fill, ReLU-backward epilogue, and conv1's
+                  weight/bias gradient as a second tensor-core GEMM over tiles staged by the epilogue
+    conv2_wgrad   tcgen05 split-K over pixels (+ column-sum kernel for the bias gradient, side branch)
+    fused allreduce + 1/N + Adadelta/Adam update, bucket 0 and bucket 1   csrc/comm/fused_allreduce.cu
+
+Gradients are double-buffered across steps at size > 1 (two captured graphs), which removes the
+one-shot kernel's exit barrier.  Loss/accuracy stay on the device: the head kernel
+writes them into a state block the trainer reads lazily.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional
+
+import torch
+
+from .. import basics
+from ..collectives import _fault_skip
+from ..keras import layers as L
+from ..keras import losses as losses_mod
+from ..ops import native
+from ..utils import nvtx
+from ..ops.gemm import EPI_ATOMIC_ADD, EPI_STORE, EPI_UNPOOL, tc_gemm
+
+
+def _declare(lib):
+    if getattr(lib, "_hvd_mnist_declared", False):
+        return
+    vp, ci, cf = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+    lib.hvd_conv1_fwd.restype = ci
+    lib.hvd_conv1_fwd.argtypes = [vp, vp, vp, vp, ci, vp, ci, vp, ci, vp, ci, vp]
+    lib.hvd_conv2_fprop.restype = ci
+    lib.hvd_conv2_fprop.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, cf, ci, vp]
+    lib.hvd_head.restype = ci
+    lib.hvd_head.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, cf, vp]
+    lib.hvd_conv2_dgrad.restype = ci
+    lib.hvd_conv2_dgrad.argtypes = [vp, vp, vp, vp, ci, ci, vp, vp, vp, vp]
+    lib.hvd_conv2_wgrad.restype = ci
+    lib.hvd_conv2_wgrad.argtypes = [vp, vp, vp, vp, ci, ci, vp]
+    lib.hvd_conv1_wgrad.restype = ci
+    lib.hvd_conv1_wgrad.argtypes = [vp, vp, vp, vp, ci, vp]
+    lib.hvd_colsum64.restype = ci
+    lib.hvd_colsum64.argtypes = [vp, vp, ctypes.c_longlong, vp]
+    lib._hvd_mnist_declared = True
+
+
+def matches(model) -> bool:
+    """True when ``model`` is exactly the reference CNN on 28x28x1 inputs."""
+    ls = getattr(model, "layers", None)
+    if not ls or len(ls) != 8 or tuple(model.input_shape) != (28, 28, 1):
+        return False
+    c1, c2, mp, d1, fl, f1, d2, f2 = ls
+    ok = (isinstance(c1, L.Conv2D) and c1.filters == 32 and c1.kernel_size == (3, 3) and c1.activation == "relu"
+          and c1.padding == "valid" and c1.strides == (1, 1) and c1.use_bias
+          and isinstance(c2, L.Conv2D) and c2.filters == 64 and c2.kernel_size == (3, 3) and c2.activation == "relu"
+          and c2.padding == "valid" and c2.strides == (1, 1) and c2.use_bias
+          and isinstance(mp, L.MaxPooling2D) and mp.pool_size == (2, 2) and mp.strides == (2, 2)
+          and isinstance(d1, L.Dropout) and isinstance(fl, L.Flatten)
+          and isinstance(f1, L.Dense) and f1.units == 128 and f1.activation == "relu" and f1.use_bias
+          and isinstance(d2, L.Dropout)
+          and isinstance(f2, L.Dense) and f2.units == 10 and f2.activation == "softmax" and f2.use_bias)
+    return bool(ok)
+
+
+def maybe_engine(model):
+    """Return a ``MnistEngine`` for ``model`` or None (generic torch-autograd path)."""
+    if os.environ.get("HVD_ENGINE", "native") != "native":
+        return None
+    if model.device.type != "cuda" or not matches(model):
+        return None
+    name = losses_mod.loss_name(model.loss) if model.loss is not None else ""
+    if "categorical_crossentropy" not in name or getattr(model.loss, "from_logits", False):
+        return None
+    if torch.cuda.get_device_capability(model.device)[0] < 10:
+        return None                      # tcgen05/TMEM kernels need sm_100a
+    return MnistEngine(model)
+
+
+class _StepResult:
+    """Handle returned by ``train_host_batch_async``: ``result()`` -> (loss, accuracy) floats."""
+
+    def __init__(self, engine, slot):
+        self._e, self._i = engine, slot
+
+    def result(self):
+        self._e._ring_ev[self._i].synchronize()
+        v = self._e._pin_ring[self._i]
+        return float(v[0]), float(v[1])
+
+
+class MnistEngine:
+    name = "native-sm100a (tcgen05/TMA kernels, CUDA graph)"
+
+    def __init__(self, model, max_batch: int = 128):
+        self.m = model
+        self.lib = native.cuda_lib(required=True)
+        _declare(self.lib)
+        self.dev = model.device
+        self.Bmax = max_batch
+        ar = model.arena
+        c1, c2, _mp, d1, _fl, f1, d2, f2 = model.layers
+        self.names = {"c1": c1.name, "c2": c2.name, "f1": f1.name, "f2": f2.name}
+        self.keep1, self.keep2 = 1.0 - d1.rate, 1.0 - d2.rate
+        B, dev = max_batch, self.dev
+        f32 = dict(dtype=torch.float32, device=dev)
+        # inputs are double-buffered by step parity (like the gradients): the H2D copy of batch t+1 can
+        # land while the graph of step t is still reading batch t
+        self.x_bufs = [torch.zeros(B, 28 * 28, **f32) for _ in range(2)]
+        self.y_bufs = [torch.zeros(B, dtype=torch.int64, device=dev) for _ in range(2)]
+        self.x_in, self.y_in = self.x_bufs[0], self.y_bufs[0]     # parity 0 (also used by eval / predict)
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._ev_in = [torch.cuda.Event(), torch.cuda.Event()]        # H2D of parity p finished
+        self._ev_done = [torch.cuda.Event(), torch.cuda.Event()]      # step that read parity p finished
+        self._pin_ring = torch.zeros(16, 2, dtype=torch.float32).pin_memory()
+        self._ring_ev = [torch.cuda.Event() for _ in range(16)]
+        # HVD_DEBUG_GUARD=1: every activation buffer sits between two sentinel-filled red zones that
+        # check_guards() verifies (compute-sanitizer is not available on every pool; this is the own check)
+        self._guards = [] if os.environ.get("HVD_DEBUG_GUARD", "0") == "1" else None
+        self.a1 = self._alloc("a1", (B, 26, 26, 32), torch.float32)
+        self.p2 = self._alloc("p2", (B, 9216), torch.float32)
+        self.mask2 = self._alloc("mask2", (B, 9216), torch.uint8)
+        self.h_pre = self._alloc("h_pre", (B, 128), torch.float32).zero_()
+        self.dh_pre = self._alloc("dh_pre", (B, 128), torch.float32)
+        self.dy2 = self._alloc("dy2", (B, 24, 24, 64), torch.float32)
+        self.probs = self._alloc("probs", (B, 10), torch.float32)
+        self._pin_x = torch.empty(B, 28 * 28, dtype=torch.float32).pin_memory()
+        self._pin_y = torch.empty(B, dtype=torch.int64).pin_memory()
+        self._pin_out = torch.zeros(2, dtype=torch.float32).pin_memory()
+        # StepState: step, loss_sum, correct_sum, last_loss, last_correct, seed, ring idx pads
+        self.state = torch.zeros(8, dtype=torch.int32, device=dev)
+        seed = (model._seed if model._seed is not None else int.from_bytes(os.urandom(3), "little")) & 0x7FFFFFFF
+        rank = basics.rank() if basics.is_initialized() else 0
+        self.state[5] = (seed * 2654435761 + 97 * rank + 1) & 0x7FFFFFFF     # per-rank dropout masks
+        self.state_f = self.state.view(torch.float32)
+        self._graphs = {}
+        self._host_step = 0
+        self._parity = 0
+        self.side = torch.cuda.Stream(device=dev)
+        self.side2 = torch.cuda.Stream(device=dev)
+        self._ev_fork = torch.cuda.Event()
+        self._ev_dx = torch.cuda.Event()
+        self._ev_b = torch.cuda.Event()
+        self._ev_b0 = torch.cuda.Event()
+        opt = model.optimizer
+        self.fused = getattr(opt, "_fused", None)
+        # HVD_BUCKET_MODE=tail: ONE bucket reduced + updated after the whole backward.
+        # =overlap: bucket 0 = dense layers (98% of the bytes) goes to a side stream as soon as dense1's dW is
+        # done, while the conv backward runs.  The conv backward CTAs fill an SM's registers and shared memory,
+        # so the overlap only works if some SMs are left free for the bucket's CTAs: HVD_RESERVE_SMS (default
+        # 16) SMs are kept out of the dgrad/wgrad split and bucket 0 runs with two CTAs on each of them.
+        # Measured: tail wins at 1 GPU (79.6 vs 87.7 us/step without a reservation) and at 2 GPUs (110 us/step
+        # vs 134 / 115 with 16 / 24 SMs reserved), so tail is the default; overlap stays selectable.
+        mode = os.environ.get("HVD_BUCKET_MODE", "tail")
+        self._bucket_mode = mode if mode in ("tail", "overlap") else "tail"
+        reserve = int(os.environ.get("HVD_RESERVE_SMS", 16)) if self._bucket_mode == "overlap" else 0
+        d_def, w_def = (110, 38) if reserve == 0 else (max(148 - reserve - 32, 8), 32)
+        self._dgrad_ctas = int(os.environ.get("HVD_DGRAD_CTAS", d_def))     # dgrad and wgrad run side by side: split the SMs
+        self._wgrad_ctas = int(os.environ.get("HVD_WGRAD_CTAS", w_def))
+        if hasattr(opt, "set_bucket_cuts") and self.fused is not None:
+            opt.set_bucket_cuts([f"{self.names['f1']}/kernel"] if self._bucket_mode == "overlap" else [])
+            self.fused = opt._fused
+            if reserve > 0 and not basics.state().config.comm_ctas:
+                self.fused.ctas[0] = min(self.fused.ctas[0], 2 * reserve)
+        cfg = basics.state().config
+        self._fault = cfg.parsed_fault() if cfg is not None else None
+        self._debug = cfg is not None and bool(cfg.debug_checksum or cfg.debug_poison)
+        self.use_graph = os.environ.get("HVD_NO_GRAPH", "0") != "1" and self.fused is not None
+        if self.fused is not None:
+            opt._defer_push = True           # hyper-parameter rows are written at step start (see _run_step)
+        self.launches_per_step = 8 + (len(self.fused.buckets) if self.fused is not None else 0)
+
+    # ------------------------------------------------------------------ helpers
+    _GUARD_BYTES = 4096
+
+    def _alloc(self, name, shape, dtype):
+        n = 1
+        for d in shape:
+            n *= d
+        if self._guards is None:
+            return torch.empty(shape, dtype=dtype, device=self.dev)
+        esz = torch.empty(0, dtype=dtype).element_size()
+        gb = self._GUARD_BYTES
+        raw = torch.full((2 * gb + n * esz,), 0xA5, dtype=torch.uint8, device=self.dev)
+        self._guards.append((name, raw, gb, n * esz))
+        return raw[gb:gb + n * esz].view(dtype).view(shape)
+
+    def check_guards(self):
+        """Raise if any kernel wrote outside its activation buffer (HVD_DEBUG_GUARD=1 only)."""
+        if self._guards is None:
+            raise RuntimeError("guards are off: set HVD_DEBUG_GUARD=1 before the model is compiled")
+        torch.cuda.synchronize(self.dev)
+        for name, raw, gb, nb in self._guards:
+            for side, zone in (("below", raw[:gb]), ("above", raw[gb + nb:])):
+                bad = (zone != 0xA5).nonzero()
+                if bad.numel():
+                    raise RuntimeError(f"out-of-bounds write {side} buffer '{name}': {bad.numel()} byte(s), "
+                                       f"first at offset {int(bad[0])} of the red zone")
+        return True
+
+    def _chk(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what} failed with code {rc}")
+
+    _SKIP = set(filter(None, os.environ.get("HVD_ABLATE", "").split(",")))   # profiling only: drop kernels from the step
+
+    def _s(self):
+        return torch.cuda.current_stream(self.dev).cuda_stream
+
+    def _p(self, key, short):
+        return self.m.arena.param(f"{self.names[key]}/{short}")
+
+    def _g(self, key, short, which):
+        return self.m.arena.grad(f"{self.names[key]}/{short}", which)
+
+    def weights_changed(self):
+        pass                                  # kernels read the arena directly; nothing is cached
+
+    # ------------------------------------------------------------------ forward
+    def _forward(self, B: int, training: bool, which: Optional[int] = None):
+        self._forward_conv(B, training, which)
+        self._forward_dense(B)
+
+    def _forward_dense(self, B: int):
+        if "d1fwd" not in self._SKIP:
+            tc_gemm(self.p2, self._p("f1", "kernel"), B, 128, 9216, a_mn=False, b_mn=True, bn=128,
+                    k_split=int(os.environ.get('HVD_D1_KSPLIT', 32)), epilogue=EPI_ATOMIC_ADD, out=self.h_pre,
+                    stream=self._s())
+
+    def _forward_conv(self, B: int, training: bool, which: Optional[int] = None):
+        lib, s = self.lib, self._s()
+        za = zb = None
+        na = nb = 0
+        if which is not None:
+            # ranges accumulated with red.add this step: the dense2/bias1 grads in front of dense_1/kernel
+            # and the conv grads behind it (the arena is in backward-ready order)
+            ar = self.m.arena
+            g = ar.grad_bufs[which]
+            na = ar.spec(f"{self.names['f1']}/kernel").offset
+            first_conv = ar.spec(f"{self.names['c2']}/bias").offset
+            nb = ar.n - first_conv
+            za, zb = g.data_ptr(), g.data_ptr() + 4 * first_conv
+        xin = self.x_bufs[which or 0]
+        if "conv1_fwd" not in self._SKIP: self._chk(lib.hvd_conv1_fwd(xin.data_ptr(), self._p("c1", "kernel").data_ptr(),
+                                    self._p("c1", "bias").data_ptr(), self.a1.data_ptr(), B, za, na, zb, nb,
+                                    self.state.data_ptr(), int(which is not None), s), "conv1_fwd")
+        if "fprop" not in self._SKIP: self._chk(lib.hvd_conv2_fprop(self.a1.data_ptr(), self._p("c2", "kernel").data_ptr(),
+                                      self._p("c2", "bias").data_ptr(), self.p2.data_ptr(), self.mask2.data_ptr(),
+                                      self.state.data_ptr(), B, int(training), self.keep1, 0, s), "conv2_fprop")
+
+    def _head(self, B: int, training: bool, backward: bool, which: int = 0, probs: bool = False):
+        gp = (lambda k, sh: self._g(k, sh, which).data_ptr()) if backward else (lambda k, sh: None)
+        if "head" not in self._SKIP: self._chk(self.lib.hvd_head(self.h_pre.data_ptr(), self._p("f1", "bias").data_ptr(),
+                                    self._p("f2", "kernel").data_ptr(), self._p("f2", "bias").data_ptr(),
+                                    self.y_bufs[which if backward else 0].data_ptr(), self.dh_pre.data_ptr(), gp("f2", "kernel"),
+                                    gp("f2", "bias"), gp("f1", "bias"),
+                                    self.probs.data_ptr() if probs else None, self.state.data_ptr(), B,
+                                    int(training), int(backward), self.keep2, self._s()), "head")
+
+    # ------------------------------------------------------------------ the training step
+    # One step = one captured graph with three parts:
+    #   A: conv1_fwd, conv2_fprop
+    #   B: dense1 fwd, head, then dense1 dW || dense1 dX
+    #   [bucket 0: fused allreduce+update of the dense layers (98% of the bytes), forked onto the side stream]
+    #   C: conv2_dgrad(+conv1 wgrad) || conv2_wgrad(+bias grad), then bucket 1 (conv layers); join.
+    # (Splitting the step into three graphs so that bucket 0 also overlaps the NEXT step's part A was
+    # measured and lost: 148 vs 136 us/step at 2 GPUs - three replays plus the out-of-graph launch made
+    # the host the bottleneck.  Gradients and hyper-parameters stay double-buffered by step parity.)
+    def _part_a(self, B: int, which: int):
+        self._forward_conv(B, True, which)
+
+    def _part_b(self, B: int, which: int):
+        main = torch.cuda.current_stream(self.dev)
+        self._forward_dense(B)
+        self._head(B, True, True, which)
+        self._ev_fork.record(main)
+        self.side2.wait_event(self._ev_fork)
+        with torch.cuda.stream(self.side2):
+            if "dw" not in self._SKIP:
+                tc_gemm(self.p2, self.dh_pre, 9216, 128, B, a_mn=True, b_mn=True, bn=128, epilogue=EPI_STORE,
+                        out=self._g("f1", "kernel", which), stream=self.side2.cuda_stream)
+        if "dx" not in self._SKIP:
+            tc_gemm(self.dh_pre, self._p("f1", "kernel"), B, 9216, 128, a_mn=False, b_mn=False, bn=64,
+                    epilogue=EPI_UNPOOL, out=self.dy2.view(-1, 64), mask=self.mask2, scale=1.0 / self.keep1,
+                    stream=self._s())
+        main.wait_stream(self.side2)
+
+    def _part_c(self, B: int, which: int):
+        lib, fused = self.lib, self.fused
+        main = torch.cuda.current_stream(self.dev)
+        s = self._s()
+        self._ev_dx.record(main)
+        self.side2.wait_event(self._ev_dx)
+        with torch.cuda.stream(self.side2):
+            if "wgrad" not in self._SKIP:
+                self._chk(lib.hvd_conv2_wgrad(self.a1.data_ptr(), self.dy2.data_ptr(),
+                                              self._g("c2", "kernel", which).data_ptr(),
+                                              self._g("c2", "bias", which).data_ptr(), B, self._wgrad_ctas,
+                                              self.side2.cuda_stream), "conv2_wgrad")
+        # conv2 dgrad with conv1's ReLU backward AND conv1's weight/bias gradient fused in (da1 never
+        # touches global memory)
+        if "dgrad" not in self._SKIP:
+            self._chk(lib.hvd_conv2_dgrad(self.dy2.data_ptr(), self._p("c2", "kernel").data_ptr(), self.a1.data_ptr(),
+                                          None, B, self._dgrad_ctas, s, self.x_bufs[which].data_ptr(),
+                                          self._g("c1", "kernel", which).data_ptr(),
+                                          self._g("c1", "bias", which).data_ptr()), "conv2_dgrad")
+        main.wait_stream(self.side2)
+        if fused is not None and "b1" not in self._SKIP:
+            for i in range(1 if self._bucket_mode == "overlap" else 0, len(fused.buckets)):
+                fused.run_bucket(i, which, self._exit_barrier(), hyper_row=which)
+
+    def _exit_barrier(self) -> int:
+        return 0 if self.m.arena.n_grad_bufs == 2 else 1
+
+    def sync_params(self):
+        """Make the current stream wait for any update still running on the side stream (call before
+        anything outside the training step reads parameters or optimizer state)."""
+        torch.cuda.current_stream(self.dev).wait_stream(self.side)
+
+    def _stage_host(self, x, y):
+        """Enqueue the H2D copy of one host batch into the input buffers of the NEXT step's parity on the
+        copy stream (from the caller's memory when it is already pinned, else through a pinned staging
+        pair) and make the main stream wait for it.  Returns the batch size."""
+        import numpy as np
+        xt = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+        yt = torch.from_numpy(np.ascontiguousarray(y))
+        if yt.ndim == 2:
+            yt = yt.argmax(dim=1)
+        yt = yt.to(torch.int64)
+        B = xt.shape[0]
+        if B > self.Bmax:
+            raise ValueError(f"batch {B} exceeds the engine's max batch {self.Bmax}")
+        w = self._which()
+        main = torch.cuda.current_stream(self.dev)
+        cs = self.copy_stream
+        if not xt.is_pinned() or not yt.is_pinned():
+            cs.synchronize()                      # the pinned staging pair is about to be overwritten
+            self._pin_x[:B].copy_(xt.reshape(B, -1))
+            self._pin_y[:B].copy_(yt)
+            xt, yt = self._pin_x[:B], self._pin_y[:B]
+        cs.wait_event(self._ev_done[w])           # the step that last read this parity's buffers is finished
+        with torch.cuda.stream(cs):
+            self.x_bufs[w][:B].copy_(xt.reshape(B, -1), non_blocking=True)
+            self.y_bufs[w][:B].copy_(yt, non_blocking=True)
+            self._ev_in[w].record(cs)
+        main.wait_event(self._ev_in[w])
+        return B
+
+    def _which(self) -> int:
+        return self._parity if self.m.arena.n_grad_bufs == 2 else 0
+
+    def train_host_batch_async(self, x, y):
+        """Pipelined end-to-end step from HOST arrays: H2D of this batch (copy stream), the step's graph,
+        and an 8-byte D2H of (loss, accuracy) into a pinned ring - all enqueued without blocking.  Returns a
+        handle; ``handle.result()`` waits for THAT step only.  Calling it one step late lets the H2D copy
+        of batch t+1 overlap the compute of step t."""
+        B = self._stage_host(x, y)
+        self._run_step(B)
+        i = self._host_step % 16
+        main = torch.cuda.current_stream(self.dev)
+        self._pin_ring[i].copy_(self.state_f[3:5], non_blocking=True)
+        self._ring_ev[i].record(main)
+        return _StepResult(self, i)
+
+    def train_host_lazy(self, x, y):
+        """fit()'s path: pipelined H2D + step, returning DEVICE scalars (no host sync at all)."""
+        B = self._stage_host(x, y)
+        self._run_step(B)
+        return self.state_f[3], self.state_f[4]
+
+    def train_host_batch(self, x, y):
+        """Blocking end-to-end step from HOST arrays; returns (loss, accuracy) as Python floats."""
+        return self.train_host_batch_async(x, y).result()
+
+    def train_step(self, x: torch.Tensor, y: torch.Tensor):
+        B = x.shape[0]
+        if B > self.Bmax:
+            raise ValueError(f"batch {B} exceeds the engine's max batch {self.Bmax}")
+        if y.ndim == 2:
+            y = y.argmax(dim=1)
+        w = self._which()
+        self.x_bufs[w][:B].copy_(x.reshape(B, -1), non_blocking=True)
+        self.y_bufs[w][:B].copy_(y.to(torch.int64), non_blocking=True)
+        self._run_step(B)
+        # Device scalars, read lazily by the trainer (no host sync, no extra launch).  They are views
+        # of the engine's state block: valid until the next step overwrites them - consumers (the fit
+        # loop's device-side running sums, callbacks calling float()) use them immediately.
+        return self.state_f[3], self.state_f[4]
+
+    def _run_step(self, B: int):
+        opt = self.m.optimizer
+        fused = self.fused
+        if hasattr(opt, "begin_step"):
+            opt.begin_step()
+        if fused is not None:
+            fused.ctx.check_error()          # host watchdog (reads one pinned word; no sync)
+            if self._fault is not None and _fault_skip():   # HVD_FAULT_INJECT=rank:step: this rank skips the step
+                return
+        which = self._which()
+        main = torch.cuda.current_stream(self.dev)
+        nvtx.push("hvd.step")
+        if fused is not None and (opt._hyper_dirty > 0 or opt.kind == 3 or getattr(opt, "decay", 0.0) > 0.0):
+            # this step's row of the hyper-parameter block (LR changed by a callback, Adam's lr_t, LR decay);
+            # nothing in flight reads this row: its last readers were step t-2's update kernels
+            opt._next_slot = which
+            opt._push_hyper()
+            opt._hyper_dirty = max(0, opt._hyper_dirty - 1)
+        if self.use_graph:
+            g = self._graphs.get((B, which))
+            if g is None:
+                g = self._graphs[(B, which)] = self._capture(B, which)
+            g.replay()
+        else:
+            self._whole_step(B, which)
+            if fused is None:
+                if which != 0:
+                    raise RuntimeError("unfused optimizer path expects a single gradient buffer")
+                opt.apply_gradients(self.m.arena)
+        self._ev_done[which].record(main)
+        if fused is not None:
+            opt.iterations += 1
+            self._parity ^= 1 if self.m.arena.n_grad_bufs == 2 else 0
+            if self._debug:
+                opt._debug_after_step(self.m.arena, which)
+        self._host_step += 1
+        nvtx.pop()
+
+    def _whole_step(self, B: int, which: int):
+        """Enqueue the whole step on the current stream (capturable): A, B, bucket 0 forked onto the side
+        stream, C, join."""
+        main = torch.cuda.current_stream(self.dev)
+        fused = self.fused
+        self._part_a(B, which)
+        self._part_b(B, which)
+        forked = False
+        if fused is not None and "b0" not in self._SKIP and self._bucket_mode == "overlap":
+            # bucket 0 (dense layers, 98% of the bytes) is complete: reduce + update it on the side stream
+            # while the conv backward runs.  It rewrites dense_1/kernel, which dX (end of part B) has
+            # finished reading by now.
+            self._ev_b.record(main)
+            self.side.wait_event(self._ev_b)
+            fused.run_bucket(0, which, self._exit_barrier(), stream=self.side, hyper_row=which)
+            forked = True
+        self._part_c(B, which)
+        if forked:
+            main.wait_stream(self.side)
+
+    def _capture(self, B: int, which: int):
+        import gc
+        gc.collect()                      # a stale CUDAGraph finalised mid-capture would invalidate the capture
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        cap = torch.cuda.Stream(device=self.dev)
+        cap.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.graph(g, stream=cap, capture_error_mode="thread_local"):
+            self._whole_step(B, which)
+        torch.cuda.current_stream(self.dev).wait_stream(cap)
+        return g
+
+    # ------------------------------------------------------------------ eval / predict
+    def eval_step(self, x: torch.Tensor, y: torch.Tensor):
+        B = x.shape[0]
+        self.sync_params()
+        if y.ndim == 2:
+            y = y.argmax(dim=1)
+        self.x_in[:B].copy_(x.reshape(B, -1), non_blocking=True)
+        self.y_in[:B].copy_(y.to(torch.int64), non_blocking=True)
+        self._forward(B, False)
+        self._head(B, False, False)
+        return self.state_f[3].clone(), self.state_f[4].clone()
+
+    def predict(self, x: torch.Tensor):
+        B = x.shape[0]
+        self.sync_params()
+        self.x_in[:B].copy_(x.reshape(B, -1), non_blocking=True)
+        self.y_in[:B].zero_()
+        self._forward(B, False)
+        self._head(B, False, False, probs=True)
+        return self.probs[:B].clone()
