@@ -63,9 +63,28 @@ def ncu_extract(rep, name):
             w.writerow([row[i][:90] for i in idx])
 
 
+def launches_from_report(rep):
+    """launches_step.csv from a --set full report of one eager (HVD_NO_GRAPH=1) step."""
+    r = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True)
+    rows = list(csv.reader(r.stdout.splitlines()))
+    if len(rows) < 3:
+        return
+    hdr, units = rows[0], rows[1]
+    ki, ti = hdr.index("Kernel Name"), hdr.index("gpu__time_duration.sum")
+    with open(os.path.join(OUT, "launches_step.csv"), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["kernel", "device_time_us (ncu, cold cache, serialised)"])
+        for row in rows[2:]:
+            t = float(row[ti].replace(",", "")) / (1000.0 if units[ti] in ("ns", "nsecond") else 1.0)
+            w.writerow([row[ki][:100], f"{t:.2f}"])
+
+
 def launches():
     src = os.path.join(ROOT, "gpurun_out", "launches.csv")
     if not os.path.exists(src):
+        reps = sorted(glob.glob(os.path.join(ROOT, "gpurun_out", "prof_step*.ncu-rep")))
+        if reps:
+            launches_from_report(reps[-1])
         return
     rows = [r for r in csv.reader(open(src)) if len(r) > 5]
     hdr = rows[0]

@@ -297,4 +297,15 @@ extern "C" int hvd_can_access_peer(int dev, int peer) {
 extern "C" int hvd_memcpy_d2d(void* dst, const void* src, long long bytes, void* stream) {
   return (int)cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
 }
+// Asynchronous copy in any direction on `stream` (the engine's per-step input staging from pinned host
+// memory and its 8-byte result read-back: one ctypes call instead of a framework copy under a stream guard).
+extern "C" int hvd_memcpy_async(void* dst, const void* src, long long bytes, void* stream) {
+  return (int)cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, (cudaStream_t)stream);
+}
+// 1 if `p` is page-locked host memory known to the CUDA runtime (safe source for a truly asynchronous H2D copy).
+extern "C" int hvd_host_is_pinned(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return a.type == cudaMemoryTypeHost ? 1 : 0;
+}
 extern "C" const char* hvd_cuda_error_string(int e) { return cudaGetErrorString((cudaError_t)e); }

@@ -109,6 +109,8 @@ int hvd_ipc_open(const void* h64, void** p);
 int hvd_ipc_close(void* p);
 int hvd_can_access_peer(int dev, int peer);
 int hvd_memcpy_d2d(void* dst, const void* src, long long bytes, void* stream);
+int hvd_memcpy_async(void* dst, const void* src, long long bytes, void* stream);   /* any direction (cudaMemcpyDefault) */
+int hvd_host_is_pinned(const void* p);
 const char* hvd_cuda_error_string(int e);
 
 /* tcgen05 TF32 GEMM, D[M,N] = A*B.  A: [M][K] (a_mn=0) or [K][M] (a_mn=1); B: [N][K] or [K][N].
@@ -130,6 +132,10 @@ int hvd_conv2_fprop(const float* a1, const float* w2, const float* bias2, float*
 int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels, float* dh_pre,
              float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B, int training, int backward,
              float keep, void* stream);
+/* hvd_head plus an optional page-locked host ring [16][4]: a training step publishes (loss, accuracy, step) there. */
+int hvd_head_ex(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels, float* dh_pre,
+                float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B, int training, int backward,
+                float keep, float* host_ring, void* stream);
 /* da1 may be NULL.  With x != NULL the conv1 weight/bias gradients are accumulated (red.add) into
  * g_w1 [9][32] / g_b1 [32] by the same kernel (tensor-core GEMM over staged tiles; no da1 round trip). */
 int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a1, float* da1, int B, int ctas, void* stream,
