@@ -48,7 +48,8 @@ __global__ void __launch_bounds__(128, 1) mma_probe_kernel(int iters, int n_acc,
 
 }  // namespace
 
-extern "C" int hvd_mma_probe(int MN, int iters, int n_acc, int a_bytes_step, int ctas, long long* out, cudaStream_t stream) {
+extern "C" int hvd_mma_probe(int MN, int iters, int n_acc, int a_bytes_step, int ctas, long long* out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
   const int smem = 65536 + 32768 + 1024 + 256;
   auto launch = [&](auto kern) -> int {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);

@@ -140,9 +140,19 @@ int hvd_head_ex(float* h_pre, const float* b1, const float* w2, const float* b2,
  * g_w1 [9][32] / g_b1 [32] by the same kernel (tensor-core GEMM over staged tiles; no da1 round trip). */
 int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a1, float* da1, int B, int ctas, void* stream,
                     const float* x, float* g_w1, float* g_b1);
+/* g_w [3][3][32][64] and g_b [64] are ACCUMULATED (red.add): zero them first.  ctas <= 0 picks a default. */
 int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream);
 int hvd_conv1_wgrad(const float* x, const float* da1, float* g_w, float* g_b, int B, void* stream);
 int hvd_colsum64(const float* m, float* out, long long rows, void* stream);
+
+/* Bring-up / profiling aids (bench/mma_probe.py, bench/desc_probe.py, bench/conv_bwd_timing.py).
+ * hvd_mma_probe: cycles for `iters` tcgen05.mma of shape M x N x 8 (MN = (M << 16) | N) rotating over n_acc
+ * accumulators; out[cta] = elapsed clock64.  hvd_conv2_bwd_debug_read: the 64 phase timers CTA 0 of the last
+ * conv2 dgrad launch recorded. */
+int hvd_mma_probe(int MN, int iters, int n_acc, int a_bytes_step, int ctas, long long* out, void* stream);
+int hvd_conv2_bwd_debug_read(long long* out64);
+int hvd_desc_probe(const float* Ag, const float* Bg, float* D, int a_mn, int rows_a, int shift_rows, unsigned lbo,
+                   unsigned sbo, int base_offset, void* stream);
 
 /* Dense layer forward y = act(x*W + bias) as a split-K tcgen05 GEMM (keras Dense, reference
  * mnist_keras.py:79,81).  x: [M][K], W: [K][N] (Keras layout), y: [M][N]; relu: 0/1; K and N must be
