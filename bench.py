@@ -200,8 +200,8 @@ def run_ours(args):
         torch.cuda.synchronize()
         hvd.barrier()
         # Public API, pipelined by one step: every step copies ITS batch from pinned host memory to the
-        # device and ITS (loss, accuracy, step) lands in pinned host memory (written by the step's head
-        # kernel, 12 bytes); the result of step t is awaited while step t+1 is already enqueued, so the H2D
+        # device and ITS (loss, accuracy, step) lands in pinned host memory (written by a kernel of the
+        # step's backward, 12 bytes); the result of step t is awaited while step t+1 is already enqueued, so the H2D
         # copy of batch t+1 overlaps the compute of step t.
         t0 = time.perf_counter()
         pending = None

@@ -370,6 +370,8 @@ struct Params {
   int B, n_strips, strips_per_cta;
   float* g_w;                               // [288][64]
   float* g_b;                               // [64]
+  const StepState* st;                      // optional: publish the step's (loss, accuracy, step) ...
+  float* host_ring;                         // ... into this page-locked host ring [16][4]
 };
 
 __global__ void __launch_bounds__(256, 1)
@@ -434,6 +436,15 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         tc::mma_commit(&empty[s]);
       }
       tc::mma_commit(accf);
+    }
+  } else if (warp == 3) {
+    // The head kernel finished long ago (stream order): hand the step's result to the host from here, off
+    // the critical path.  ONE aligned 16-byte store = one posted PCIe write, so the host never sees the step
+    // number without the values; nothing on the compute stream waits for it.
+    if (blockIdx.x == 0 && lane == 0 && p.host_ring != nullptr) {
+      const unsigned step = p.st->step;
+      *reinterpret_cast<float4*>(p.host_ring + (step & 15u) * 4) =
+          make_float4(p.st->last_loss, p.st->last_correct, __uint_as_float(step), 0.f);
     }
   } else if (warp >= 4 && ns > 0) {
     // ---- while the tensor core works: conv2's bias gradient = column sums of the dY2 tile (every dY2 pixel
@@ -519,7 +530,8 @@ extern "C" int hvd_conv2_bwd_debug_read(long long* out64) {
   return (int)cudaMemcpyFromSymbol(out64, g_bwd_dbg, sizeof(long long) * 64);
 }
 
-extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream) {
+extern "C" int hvd_conv2_wgrad_ex(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream,
+                                  const void* step_state, float* host_ring) {
   CUtensorMap tmA, tmG;
   {
     uint64_t dims[4] = {32, 26, 26, (uint64_t)B};
@@ -545,5 +557,11 @@ extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, fl
   p.strips_per_cta = (p.n_strips + ctas - 1) / ctas;
   ctas = (p.n_strips + p.strips_per_cta - 1) / p.strips_per_cta;
   p.g_w = g_w; p.g_b = g_b;
+  p.st = reinterpret_cast<const mnist::StepState*>(step_state);
+  p.host_ring = step_state ? host_ring : nullptr;
   return (int)tc::launch_pdl(wg::conv2_wgrad_kernel, dim3(ctas), dim3(256), wg::SMEM_BYTES, (cudaStream_t)stream, tmA, tmG, p);
+}
+
+extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream) {
+  return hvd_conv2_wgrad_ex(a1, dy2, g_w, g_b, B, ctas, stream, nullptr, nullptr);
 }

@@ -21,8 +21,7 @@ struct StepState {
   float last_loss;          // mean loss of the latest batch
   float last_correct;       // correct count of the latest batch
   unsigned int seed;
-  unsigned int head_done;   // CTAs of the head kernel that have added their rows (last one publishes the result)
-  unsigned int pad1;
+  unsigned int pad0, pad1;
 };
 
 // Philox4x32-10 (Salmon et al.), the counter-based RNG TF/Keras dropout is built on.  Masks

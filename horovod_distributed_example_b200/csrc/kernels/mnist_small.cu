@@ -81,7 +81,6 @@ struct HeadParams {
   float* g_w2; float* g_b2; float* g_b1;   // gradient slots in the arena (accumulated: zeroed by the prologue)
   float* probs;               // [B,10] out (predict / eval), may be null
   StepState* st;
-  float* host_ring;           // page-locked host memory [16][4] (loss, accuracy, step as bits, -), may be null
 };
 
 constexpr int HEAD_ROWS = 8;  // batch rows per CTA: one warp per row
@@ -167,20 +166,6 @@ __global__ void __launch_bounds__(256) head_kernel(HeadParams p) {
   }
   __syncthreads();
   if (!p.backward) return;
-  if (p.host_ring && tid == 0) {
-    // Publish the step's (loss, accuracy) straight into page-locked host memory: the last CTA to add its rows
-    // writes (loss, accuracy, step number) into slot step % 16; the host polls the step word.  No copy node sits between two
-    // steps' graphs on the stream, and nothing waits on an event.
-    __threadfence();
-    if (atomicAdd(&p.st->head_done, 1u) == gridDim.x - 1) {
-      p.st->head_done = 0;
-      __threadfence();
-      const float l = atomicAdd(&p.st->last_loss, 0.f), c = atomicAdd(&p.st->last_correct, 0.f);
-      // ONE aligned 16-byte store = one posted PCIe write: the host never sees the step number without the
-      // values, and this thread does not wait for a system-scope fence on the step's critical path
-      *reinterpret_cast<float4*>(p.host_ring + (step & 15u) * 4) = make_float4(l, c, __uint_as_float(step), 0.f);
-    }
-  }
   // dW2[j][k] += sum_rows h[r][j] dl[r][k];  db2[k] += sum_rows dl[r][k]
   for (int o = tid; o < HID * NCLS + NCLS; o += 256) {
     float acc = 0.f;
@@ -291,22 +276,13 @@ extern "C" int hvd_conv1_fwd(const float* x, const float* w, const float* bias, 
   return (int)tc::launch_pdl(conv1_fwd_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, w, bias, a1, B, pro);
 }
 
-// host_ring: optional page-locked host buffer of 16 x 4 floats; in a training step (backward != 0) the kernel
-// writes (mean loss, accuracy, step number) of the step into slot step % 16 (see head_kernel).
-extern "C" int hvd_head_ex(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels,
-                           float* dh_pre, float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B,
-                           int training, int backward, float keep, float* host_ring, void* stream) {
-  if (B < 1) return -1;
-  HeadParams p{B, training, backward, HEAD_ROWS, keep, h_pre, b1, w2, b2, labels, dh_pre, g_w2, g_b2, g_b1, probs,
-               reinterpret_cast<mnist::StepState*>(step_state), host_ring};
-  return (int)tc::launch_pdl(head_kernel, dim3((B + HEAD_ROWS - 1) / HEAD_ROWS), dim3(256), 0, (cudaStream_t)stream, p);
-}
-
 extern "C" int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels,
                         float* dh_pre, float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B,
                         int training, int backward, float keep, void* stream) {
-  return hvd_head_ex(h_pre, b1, w2, b2, labels, dh_pre, g_w2, g_b2, g_b1, probs, step_state, B, training, backward, keep,
-                     nullptr, stream);
+  if (B < 1) return -1;
+  HeadParams p{B, training, backward, HEAD_ROWS, keep, h_pre, b1, w2, b2, labels, dh_pre, g_w2, g_b2, g_b1, probs,
+               reinterpret_cast<mnist::StepState*>(step_state)};
+  return (int)tc::launch_pdl(head_kernel, dim3((B + HEAD_ROWS - 1) / HEAD_ROWS), dim3(256), 0, (cudaStream_t)stream, p);
 }
 
 extern "C" int hvd_conv1_wgrad(const float* x, const float* da1, float* g_w, float* g_b, int B, void* stream) {

@@ -140,27 +140,51 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int j = 0; j < 32; j++) v[j] = 0.f;
       }
-      if (row < p.M && p.epilogue == EPI_UNPOOL) {
+      if (p.epilogue == EPI_UNPOOL) {
+        // The accumulator gives each lane ONE sample's 32 channels, but consecutive samples are 147 KB apart
+        // in dY2: stored from that layout every warp store touches 32 half-filled sectors.  Transpose through
+        // shared memory (the pipeline stages are idle once the accumulator is complete) so that 8 lanes
+        // write one sample's 128 contiguous bytes and a warp store fills 16 whole sectors.
+        float* T = reinterpret_cast<float*>(smem + (warp - 4) * (32 * 33 * 4 + 32 * 9 * 4));   // [32][33] values
+        uint32_t* Mw = reinterpret_cast<uint32_t*>(T + 32 * 33);                                // [32][9] mask words
         const int f = n0 + c;                                  // flat (ph, pw, c0) with c0 in {0, 32}
         const int ph = f / (12 * 64), pw = (f / 64) % 12, c0 = f & 63;
-        const uint4* mp = reinterpret_cast<const uint4*>(p.mask + (long long)row * 9216 + f);
-        const uint4 m0 = mp[0], m1 = mp[1];
-        const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-        float* base = p.D + (((long long)row * 24 + 2 * ph) * 24 + 2 * pw) * 64 + c0;
+        {
+          uint4 m0 = make_uint4(0, 0, 0, 0), m1 = m0;          // rows past M: nothing live
+          if (row < p.M) {
+            const uint4* mp = reinterpret_cast<const uint4*>(p.mask + (long long)row * 9216 + f);
+            m0 = mp[0]; m1 = mp[1];
+          }
+          const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
 #pragma unroll
-        for (int pos = 0; pos < 4; pos++) {
-          float* d = base + ((pos >> 1) * 24 + (pos & 1)) * 64;
+          for (int j = 0; j < 32; j++) T[lane * 33 + j] = v[j] * p.scale;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float o[4];
+          for (int j = 0; j < 8; j++) Mw[lane * 9 + j] = mw[j];
+        }
+        __syncwarp();
+        const int k = lane & 7;                                // channels 4k .. 4k+3 of the chunk
+#pragma unroll 2
+        for (int i = 0; i < 8; i++) {
+          const int b = i * 4 + (lane >> 3);                   // sample inside this warp's 32 rows
+          const int grow = m0 + q * 32 + b;
+          const float t0 = T[b * 33 + 4 * k], t1 = T[b * 33 + 4 * k + 1], t2 = T[b * 33 + 4 * k + 2], t3 = T[b * 33 + 4 * k + 3];
+          const uint32_t mk = Mw[b * 9 + k];
+          if (grow < p.M) {
+            float* base = p.D + (((long long)grow * 24 + 2 * ph) * 24 + 2 * pw) * 64 + c0 + 4 * k;
+            const float tv[4] = {t0, t1, t2, t3};
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
-              const uint32_t mb = (mw[(j + e) >> 2] >> (8 * ((j + e) & 3))) & 0xff;
-              o[e] = ((mb & 4) && (int)(mb & 3) == pos) ? v[j + e] * p.scale : 0.f;
+            for (int pos = 0; pos < 4; pos++) {
+              float o[4];
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                const uint32_t mb = (mk >> (8 * e)) & 0xff;
+                o[e] = ((mb & 4) && (int)(mb & 3) == pos) ? tv[e] : 0.f;
+              }
+              *reinterpret_cast<float4*>(base + ((pos >> 1) * 24 + (pos & 1)) * 64) = make_float4(o[0], o[1], o[2], o[3]);
             }
-            *reinterpret_cast<float4*>(d + j) = make_float4(o[0], o[1], o[2], o[3]);
           }
         }
+        __syncwarp();                                          // the next column chunk reuses T / Mw
       } else if (row < p.M) {
         float* d = p.D + (long long)row * p.ldd + n0 + c;
         if (p.epilogue == EPI_ATOMIC_ADD) {

@@ -48,8 +48,6 @@ def _declare(lib):
     lib.hvd_conv2_fprop.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, cf, ci, vp]
     lib.hvd_head.restype = ci
     lib.hvd_head.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, cf, vp]
-    lib.hvd_head_ex.restype = ci
-    lib.hvd_head_ex.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, cf, vp, vp]
     lib.hvd_memcpy_async.restype = ci
     lib.hvd_memcpy_async.argtypes = [vp, vp, ctypes.c_longlong, vp]
     lib.hvd_host_is_pinned.restype = ci
@@ -58,6 +56,8 @@ def _declare(lib):
     lib.hvd_conv2_dgrad.argtypes = [vp, vp, vp, vp, ci, ci, vp, vp, vp, vp]
     lib.hvd_conv2_wgrad.restype = ci
     lib.hvd_conv2_wgrad.argtypes = [vp, vp, vp, vp, ci, ci, vp]
+    lib.hvd_conv2_wgrad_ex.restype = ci
+    lib.hvd_conv2_wgrad_ex.argtypes = [vp, vp, vp, vp, ci, ci, vp, vp, vp]
     lib.hvd_conv1_wgrad.restype = ci
     lib.hvd_conv1_wgrad.argtypes = [vp, vp, vp, vp, ci, vp]
     lib.hvd_colsum64.restype = ci
@@ -100,8 +100,8 @@ def maybe_engine(model):
 class _StepResult:
     """Handle returned by ``train_host_batch_async``: ``result()`` -> (loss, accuracy) floats.
 
-    The step's head kernel writes (loss, accuracy, step number) into a page-locked host ring; ``result()``
-    polls that slot's step word - no copy node on the stream, no event."""
+    A kernel of the step's backward (conv2 wgrad, CTA 0) writes (loss, accuracy, step number) into a
+    page-locked host ring; ``result()`` polls that slot's step word - no copy node on the stream, no event."""
 
     def __init__(self, engine, seq):
         self._e, self._seq = engine, seq
@@ -291,12 +291,12 @@ class MnistEngine:
 
     def _head(self, B: int, training: bool, backward: bool, which: int = 0, probs: bool = False):
         gp = (lambda k, sh: self._g(k, sh, which).data_ptr()) if backward else (lambda k, sh: None)
-        if "head" not in self._SKIP: self._chk(self.lib.hvd_head_ex(self.h_pre.data_ptr(), self._p("f1", "bias").data_ptr(),
+        if "head" not in self._SKIP: self._chk(self.lib.hvd_head(self.h_pre.data_ptr(), self._p("f1", "bias").data_ptr(),
                                     self._p("f2", "kernel").data_ptr(), self._p("f2", "bias").data_ptr(),
                                     self.y_bufs[which if backward else 0].data_ptr(), self.dh_pre.data_ptr(), gp("f2", "kernel"),
                                     gp("f2", "bias"), gp("f1", "bias"),
                                     self.probs.data_ptr() if probs else None, self.state.data_ptr(), B,
-                                    int(training), int(backward), self.keep2, self._ring_ptr, self._s()), "head")
+                                    int(training), int(backward), self.keep2, self._s()), "head")
 
     # ------------------------------------------------------------------ the training step
     # One step = one captured graph with three parts:
@@ -334,10 +334,11 @@ class MnistEngine:
         self.side2.wait_event(self._ev_dx)
         with torch.cuda.stream(self.side2):
             if "wgrad" not in self._SKIP:
-                self._chk(lib.hvd_conv2_wgrad(self.a1.data_ptr(), self.dy2.data_ptr(),
-                                              self._g("c2", "kernel", which).data_ptr(),
-                                              self._g("c2", "bias", which).data_ptr(), B, self._wgrad_ctas,
-                                              self.side2.cuda_stream), "conv2_wgrad")
+                # (CTA 0 of this kernel also writes the step's loss/accuracy into the pinned host ring)
+                self._chk(lib.hvd_conv2_wgrad_ex(self.a1.data_ptr(), self.dy2.data_ptr(),
+                                                 self._g("c2", "kernel", which).data_ptr(),
+                                                 self._g("c2", "bias", which).data_ptr(), B, self._wgrad_ctas,
+                                                 self.side2.cuda_stream, self.state.data_ptr(), self._ring_ptr), "conv2_wgrad")
         # conv2 dgrad with conv1's ReLU backward AND conv1's weight/bias gradient fused in (da1 never
         # touches global memory)
         if "dgrad" not in self._SKIP:
@@ -410,7 +411,7 @@ class MnistEngine:
 
     def train_host_batch_async(self, x, y):
         """Pipelined end-to-end step from HOST arrays: H2D of this batch (copy stream), the step's graph,
-        whose head kernel writes (loss, accuracy, step) into a pinned host ring - all enqueued without blocking.  Returns a
+        which writes (loss, accuracy, step) into a pinned host ring - all enqueued without blocking.  Returns a
         handle; ``handle.result()`` waits for THAT step only.  Calling it one step late lets the H2D copy
         of batch t+1 overlap the compute of step t."""
         B = self._stage_host(x, y)

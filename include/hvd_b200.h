@@ -132,16 +132,17 @@ int hvd_conv2_fprop(const float* a1, const float* w2, const float* bias2, float*
 int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels, float* dh_pre,
              float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B, int training, int backward,
              float keep, void* stream);
-/* hvd_head plus an optional page-locked host ring [16][4]: a training step publishes (loss, accuracy, step) there. */
-int hvd_head_ex(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels, float* dh_pre,
-                float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B, int training, int backward,
-                float keep, float* host_ring, void* stream);
 /* da1 may be NULL.  With x != NULL the conv1 weight/bias gradients are accumulated (red.add) into
  * g_w1 [9][32] / g_b1 [32] by the same kernel (tensor-core GEMM over staged tiles; no da1 round trip). */
 int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a1, float* da1, int B, int ctas, void* stream,
                     const float* x, float* g_w1, float* g_b1);
 /* g_w [3][3][32][64] and g_b [64] are ACCUMULATED (red.add): zero them first.  ctas <= 0 picks a default. */
 int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream);
+/* Same, and CTA 0 also publishes the training step's result: it copies (last_loss, last_correct, step) from the
+ * step-state block (written by hvd_head earlier on the stream) into slot step % 16 of `host_ring`, a page-locked
+ * host buffer of 16 x 4 floats, as one 16-byte store.  The host polls the step word. */
+int hvd_conv2_wgrad_ex(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream,
+                       const void* step_state, float* host_ring);
 int hvd_conv1_wgrad(const float* x, const float* da1, float* g_w, float* g_b, int B, void* stream);
 int hvd_colsum64(const float* m, float* out, long long rows, void* stream);
 
