@@ -61,6 +61,7 @@ struct Params {
   const float* x;             // [B,28,28] network input, for the fused conv1 weight gradient (null = off)
   float* g_w1;                // [9][32]  accumulated with red.add
   float* g_b1;                // [32]
+  int n_w, t1;                // tile ownership (see body): n_w < 0 = round-robin over the grid
 };
 
 // Row r of an MN-major staging tile (128 B per row, SWIZZLE_128B_BASE32B): 32-byte chunk c lives at
@@ -69,10 +70,13 @@ __device__ __forceinline__ float* stg_chunk(uint8_t* tile, int r, int c) {
   return reinterpret_cast<float*>(tile + r * 128 + ((c ^ (r & 3)) << 5));
 }
 
-__global__ void __launch_bounds__(384, 1)
-conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmW, Params p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+// The whole dgrad as a device function so that it can run as its own kernel or as the second phase of the
+// fused conv2 backward kernel.  `smem` is 1024-byte aligned, `tmem` an allocation of TMEM_COLS columns; every
+// thread of the CTA calls it.  It initialises its own mbarriers and ends with a __syncthreads().
+__device__ __forceinline__ void body(uint8_t* smem, const uint32_t tmem, const CUtensorMap* tmGp, const CUtensorMap* tmWp,
+                                     const Params& p) {
+  const CUtensorMap& tmG = *tmGp;
+  const CUtensorMap& tmW = *tmWp;
   uint8_t* sW = smem;
   uint8_t* sA = smem + W_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sA + STAGES * A_STAGE);
@@ -84,10 +88,29 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   uint64_t* stgf = acce + 2;           // [2] staging tile written by the epilogue
   uint64_t* stge = stgf + 2;           // [2] staging tile consumed by the tensor core
   uint64_t* w1done = stge + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w1done + 1);
   uint8_t* sStg = sA + STAGES * A_STAGE + 1024;  // the barrier block owns the 1 KB in between (keeps 1024 B alignment)
   float* sXch = reinterpret_cast<float*>(sStg + 2 * STG_BYTES);
   const bool fuse_w1 = p.x != nullptr;
+  // Which tiles this CTA owns: t_first + k * t_stride for k < t_count.  Stand-alone: round-robin over the grid.
+  // Fused kernel: the first n_w CTAs spent the first phase on wgrad strips and take only t1 tiles, the rest
+  // split the remainder evenly (contiguous ranges).
+  int t_first, t_stride, t_count;
+  {
+    const int c = (int)blockIdx.x, G = (int)gridDim.x;
+    if (p.n_w < 0) {
+      t_first = c; t_stride = G;
+      t_count = c < p.n_tiles ? (p.n_tiles - c + G - 1) / G : 0;
+    } else {
+      t_stride = 1;
+      if (c < p.n_w) { t_first = c * p.t1; t_count = p.t1; }
+      else {
+        const int rest = p.n_tiles - p.n_w * p.t1, pure = G - p.n_w, j = c - p.n_w;
+        const int t2 = rest / pure, rem = rest - t2 * pure;
+        t_first = p.n_w * p.t1 + j * t2 + (j < rem ? j : rem);
+        t_count = t2 + (j < rem ? 1 : 0);
+      }
+    }
+  }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) { tc::tma_prefetch_desc(&tmG); tc::tma_prefetch_desc(&tmW); }
@@ -101,13 +124,9 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     tc::mbar_init(w1done, 1);
     tc::fence_barrier_init();
   }
-  if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  tc::pdl_launch_dependents();
-  tc::pdl_wait();
 
   if (warp == 0) {
     if (tc::elect_one()) {
@@ -118,7 +137,8 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         for (int h = 0; h < 2; h++)
           tc::tma_load_2d(sW + (((t / 3) * 2 + h) * 3 + (t % 3)) * 4096, &tmW, wfull, 32 * h, t * 32);
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      for (int kt = 0; kt < t_count; kt++) {
+        const int tile = t_first + kt * t_stride;
         const int b = tile / TILES_PER_IMG, ybase = ((tile % TILES_PER_IMG) * TILE_STRIDE) / H1;
         for (int half = 0; half < 2; half++, it++) {
           const int s = it % STAGES;
@@ -152,7 +172,8 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       };
       tc::mbar_wait(wfull, 0);
       int it = 0, ti = 0;
-      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ti++) {
+      for (; ti < t_count; ti++) {
+        const int tile = t_first + ti * t_stride;
         const int as = ti & 1;
         const bool dbg_on = blockIdx.x == 0 && (ti == 2 || ti == 3);
         HVD_DBG_T(8 + (ti & 1) * 8);
@@ -199,7 +220,8 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     const int set = (warp - 4) >> 2;
     const int r = q * 32 + lane;               // accumulator row = raster position p0 + r
     int ti = set;
-    for (int tile = blockIdx.x + set * gridDim.x; tile < p.n_tiles; tile += 2 * gridDim.x, ti += 2) {
+    for (; ti < t_count; ti += 2) {
+      const int tile = t_first + ti * t_stride;
       const int as = ti & 1;
       const bool dbg_on = blockIdx.x == 0 && threadIdx.x == 128 && ti == 2;
       const int b = tile / TILES_PER_IMG, tt = tile % TILES_PER_IMG;
@@ -330,7 +352,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       float w[32];
       tc::tmem_ld_x32(tmem + W1_COL, w);
       tc::tmem_ld_wait();
-      if (blockIdx.x < p.n_tiles && lane < 10) {
+      if (t_count > 0 && lane < 10) {
         float* d = lane < 9 ? p.g_w1 + lane * 32 : p.g_b1;
 #pragma unroll
         for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, w[j], w[j + 1], w[j + 2], w[j + 3]);
@@ -339,6 +361,22 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   }
   tc::tc_fence_before();
   __syncthreads();
+}
+
+__global__ void __launch_bounds__(384, 1)
+conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmW, Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5;
+  if (warp == 2) tc::tmem_alloc<TMEM_COLS>(&tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
+  body(smem, tmem, &tmG, &tmW, p);
   if (warp == 2) tc::tmem_dealloc<TMEM_COLS>(tmem);
 }
 }  // namespace dg
@@ -367,27 +405,27 @@ constexpr int ACC_N = 192;
 constexpr int TMEM_COLS = 256;
 
 struct Params {
-  int B, n_strips, strips_per_cta;
+  int B, n_strips, n_w;
   float* g_w;                               // [288][64]
   float* g_b;                               // [64]
   const StepState* st;                      // optional: publish the step's (loss, accuracy, step) ...
   float* host_ring;                         // ... into this page-locked host ring [16][4]
 };
 
-__global__ void __launch_bounds__(256, 1)
-conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmG, Params p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+// Device-function form (own kernel, or first phase of the fused conv2 backward kernel): see dg::body.
+// Uses warps 0..7 only.  Strips are dealt round-robin over the first n_w CTAs: strip = blockIdx.x + i * n_w.
+__device__ __forceinline__ void body(uint8_t* smem, const uint32_t tmem, const CUtensorMap* tmAp, const CUtensorMap* tmGp,
+                                     const Params& p) {
+  const CUtensorMap& tmA = *tmAp;
+  const CUtensorMap& tmG = *tmGp;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE);
   uint64_t* full = bars;
   uint64_t* empty = bars + STAGES;
   uint64_t* accf = bars + 2 * STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accf + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int s_begin = blockIdx.x * p.strips_per_cta;
-  const int s_end = min(p.n_strips, s_begin + p.strips_per_cta);
-  const int ns = s_end - s_begin;
+  const int nw = p.n_w > 0 ? p.n_w : (int)gridDim.x;      // CTAs that take strips (the fused kernel uses a subset)
+  const int ns = (int)blockIdx.x < nw && (int)blockIdx.x < p.n_strips ? (p.n_strips - (int)blockIdx.x + nw - 1) / nw : 0;
   if (warp == 0 && lane == 0) { tc::tma_prefetch_desc(&tmA); tc::tma_prefetch_desc(&tmG); }
   if (warp == 1 && lane == 0) {
     // a stage is free again when the tensor core (1 commit) and the four bias-sum warps (1 arrive each) are done
@@ -395,7 +433,6 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tc::mbar_init(accf, 1);
     tc::fence_barrier_init();
   }
-  if (warp == 2) tc::tmem_alloc<TMEM_COLS>(tmem_slot);
   // the slack rows after each halo tile are read by the dummy 4th atom: keep them finite
   for (int i = threadIdx.x; i < STAGES * 4 * 32; i += blockDim.x)
     reinterpret_cast<float*>(smem + (i / 128) * STAGE + HALO_TX)[i % 128] = 0.f;
@@ -403,9 +440,6 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  tc::pdl_launch_dependents();
-  tc::pdl_wait();
 
   if (warp == 0) {
     if (tc::elect_one()) {
@@ -413,7 +447,7 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int s = i % STAGES;
         tc::mbar_wait(&empty[s], ((i / STAGES) & 1) ^ 1);
         tc::mbar_expect_tx(&full[s], STAGE_TX);
-        const int strip = s_begin + i;
+        const int strip = (int)blockIdx.x + i * nw;
         const int b = strip / 3, px = strip % 3;
         uint8_t* st = smem + s * STAGE;
         tc::tma_load_4d(st, &tmA, &full[s], 0, px * 8, 0, b);                      // a1 columns px*8 .. px*8+9, all 26 rows
@@ -446,7 +480,7 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       *reinterpret_cast<float4*>(p.host_ring + (step & 15u) * 4) =
           make_float4(p.st->last_loss, p.st->last_correct, __uint_as_float(step), 0.f);
     }
-  } else if (warp >= 4 && ns > 0) {
+  } else if (warp >= 4 && warp < 8 && ns > 0) {
     // ---- while the tensor core works: conv2's bias gradient = column sums of the dY2 tile (every dY2 pixel
     // is in exactly one strip; the halo rows are zeros).  Thread t reads the 16-byte chunk at position t%8 of
     // rows t/8, t/8+16, ...: r & 3 and the channel half (r >> 3) & 1 are the same for all of them, so after
@@ -491,11 +525,57 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       }
     }
   }
+  tc::fence_proxy_async();      // generic-proxy reads of the stages are ordered before whatever TMA writes there next
   tc::tc_fence_before();
   __syncthreads();
+}
+
+__global__ void __launch_bounds__(256, 1)
+conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmG, Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5;
+  if (warp == 2) tc::tmem_alloc<TMEM_COLS>(&tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
+  body(smem, tmem, &tmA, &tmG, p);
   if (warp == 2) tc::tmem_dealloc<TMEM_COLS>(tmem);
 }
 }  // namespace wg
+
+// ============================================================================ both in one launch
+// Phase 1: the first n_w CTAs reduce the wgrad strips (every CTA that takes strips pays 73 KB of red.adds
+// for its 288x64 partial result, so not all of them do).  Phase 2: all CTAs compute dgrad tiles in the same
+// shared memory and TMEM - the wgrad CTAs only t1 each, the others the rest.  Compared with two kernels side
+// by side on a fixed SM split this balances the work to within one tile per CTA, lets the red.adds drain
+// while dgrad computes, and saves a launch and a stream join.
+constexpr int FUSED_SMEM = dg::SMEM_BYTES > wg::SMEM_BYTES ? dg::SMEM_BYTES : wg::SMEM_BYTES;
+static_assert(dg::TMEM_COLS == wg::TMEM_COLS, "the two phases share one TMEM allocation");
+
+__global__ void __launch_bounds__(384, 1)
+conv2_bwd_kernel(const __grid_constant__ CUtensorMap tmA_w, const __grid_constant__ CUtensorMap tmG_w,
+                 const __grid_constant__ CUtensorMap tmG_d, const __grid_constant__ CUtensorMap tmW_d, wg::Params pw,
+                 dg::Params pd) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5;
+  if (warp == 2) tc::tmem_alloc<dg::TMEM_COLS>(&tmem_slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
+  wg::body(smem, tmem, &tmA_w, &tmG_w, pw);
+  dg::body(smem, tmem, &tmG_d, &tmW_d, pd);
+  if (warp == 2) tc::tmem_dealloc<dg::TMEM_COLS>(tmem);
+}
 
 }  // namespace
 
@@ -519,7 +599,7 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
     if (cudaFuncSetAttribute(dg::conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dg::SMEM_BYTES) != cudaSuccess) return -10;
     attr = true;
   }
-  dg::Params p{B, B * dg::TILES_PER_IMG, a1, da1, x, g_w1, g_b1};
+  dg::Params p{B, B * dg::TILES_PER_IMG, a1, da1, x, g_w1, g_b1, -1, 0};
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
   return (int)tc::launch_pdl(dg::conv2_dgrad_kernel, dim3(ctas), dim3(384), dg::SMEM_BYTES, (cudaStream_t)stream, tmG, tmW, p);
@@ -551,15 +631,59 @@ extern "C" int hvd_conv2_wgrad_ex(const float* a1, const float* dy2, float* g_w,
     attr = true;
   }
   wg::Params p;
-  p.B = B; p.n_strips = B * 3;
+  p.B = B; p.n_strips = B * 3; p.n_w = 0;
   if (ctas <= 0) ctas = 128;
   if (ctas > p.n_strips) ctas = p.n_strips;
-  p.strips_per_cta = (p.n_strips + ctas - 1) / ctas;
-  ctas = (p.n_strips + p.strips_per_cta - 1) / p.strips_per_cta;
   p.g_w = g_w; p.g_b = g_b;
   p.st = reinterpret_cast<const mnist::StepState*>(step_state);
   p.host_ring = step_state ? host_ring : nullptr;
   return (int)tc::launch_pdl(wg::conv2_wgrad_kernel, dim3(ctas), dim3(256), wg::SMEM_BYTES, (cudaStream_t)stream, tmA, tmG, p);
+}
+
+// conv2 wgrad + dgrad (+ fused conv1 wgrad) in ONE launch: g_w2 [3][3][32][64], g_b2 [64], g_w1 [9][32], g_b1 [32]
+// are accumulated (zero them first); step_state / host_ring as in hvd_conv2_wgrad_ex (may be NULL).
+extern "C" int hvd_conv2_bwd(const float* dy2, const float* w2, const float* a1, const float* x, float* g_w2, float* g_b2,
+                             float* g_w1, float* g_b1, int B, int ctas, void* stream, const void* step_state,
+                             float* host_ring, int wgrad_ctas, int wgrad_cta_tiles) {
+  CUtensorMap tmA_w, tmG_w, tmG_d, tmW_d;
+  {
+    uint64_t ad[4] = {32, 26, 26, (uint64_t)B};
+    uint64_t as[3] = {128, 26 * 128, 26 * 26 * 128};
+    uint32_t hbox[4] = {32, 10, 26, 1};
+    if (tc::make_tmap(&tmA_w, a1, 4, ad, as, hbox, true)) return -2;
+    uint64_t gd5[5] = {32, 24, 2, 24, (uint64_t)B};
+    uint64_t gs5[4] = {256, 128, 24 * 256, 24 * 24 * 256};
+    uint32_t box5[5] = {32, 8, 2, 28, 1};
+    if (tc::make_tmap(&tmG_w, dy2, 5, gd5, gs5, box5, true)) return -3;
+    uint64_t gd[4] = {64, 24, 24, (uint64_t)B};
+    uint64_t gs[3] = {256, 24 * 256, 24 * 24 * 256};
+    uint32_t box[4] = {32, dg::BOX_W, dg::BOX_H, 1};
+    if (tc::make_tmap(&tmG_d, dy2, 4, gd, gs, box)) return -4;
+    uint64_t wd[2] = {64, 288};
+    uint64_t ws[1] = {256};
+    uint32_t wb[2] = {32, 32};
+    if (tc::make_tmap(&tmW_d, w2, 2, wd, ws, wb)) return -5;
+  }
+  static bool attr = false;
+  if (!attr) {
+    if (cudaFuncSetAttribute(conv2_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_SMEM) != cudaSuccess) return -10;
+    attr = true;
+  }
+  if (ctas <= 0) ctas = 148;
+  const int n_tiles = B * dg::TILES_PER_IMG;
+  // the first n_w CTAs reduce the wgrad strips (a strip costs about 0.6 dgrad tiles) and then take t1 tiles each
+  int n_w = wgrad_ctas > 0 ? wgrad_ctas : (ctas * 48) / 148;
+  if (n_w < 1) n_w = 1;
+  if (n_w > ctas - 1) n_w = ctas > 1 ? ctas - 1 : 1;
+  int t1 = wgrad_cta_tiles >= 0 ? wgrad_cta_tiles : 2;
+  if (n_w * t1 > n_tiles) t1 = n_tiles / n_w;
+  if (ctas == 1) { n_w = 1; t1 = n_tiles; }
+  wg::Params pw;
+  pw.B = B; pw.n_strips = B * 3; pw.n_w = n_w; pw.g_w = g_w2; pw.g_b = g_b2;
+  pw.st = reinterpret_cast<const mnist::StepState*>(step_state);
+  pw.host_ring = step_state ? host_ring : nullptr;
+  dg::Params pd{B, n_tiles, a1, nullptr, x, g_w1, g_b1, n_w, t1};
+  return (int)tc::launch_pdl(conv2_bwd_kernel, dim3(ctas), dim3(384), FUSED_SMEM, (cudaStream_t)stream, tmA_w, tmG_w, tmG_d, tmW_d, pw, pd);
 }
 
 extern "C" int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream) {

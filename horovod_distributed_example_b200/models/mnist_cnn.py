@@ -56,6 +56,8 @@ def _declare(lib):
     lib.hvd_conv2_dgrad.argtypes = [vp, vp, vp, vp, ci, ci, vp, vp, vp, vp]
     lib.hvd_conv2_wgrad.restype = ci
     lib.hvd_conv2_wgrad.argtypes = [vp, vp, vp, vp, ci, ci, vp]
+    lib.hvd_conv2_bwd.restype = ci
+    lib.hvd_conv2_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, vp, vp, vp, ci, ci]
     lib.hvd_conv2_wgrad_ex.restype = ci
     lib.hvd_conv2_wgrad_ex.argtypes = [vp, vp, vp, vp, ci, ci, vp, vp, vp]
     lib.hvd_conv1_wgrad.restype = ci
@@ -197,6 +199,13 @@ class MnistEngine:
         d_def, w_def = (110, 38) if reserve == 0 else (max(148 - reserve - 32, 8), 32)
         self._dgrad_ctas = int(os.environ.get("HVD_DGRAD_CTAS", d_def))     # dgrad and wgrad run side by side: split the SMs
         self._wgrad_ctas = int(os.environ.get("HVD_WGRAD_CTAS", w_def))
+        # HVD_FUSED_BWD=1: conv2 wgrad + dgrad as ONE kernel (hvd_conv2_bwd).  Measured equal to the two kernels
+        # side by side (75.8 us/step both; the pair is bound by L2/TMA latency, not by the SM split), so the
+        # default stays the two-kernel form that the multi-GPU runs validated.
+        self._fused_bwd = os.environ.get("HVD_FUSED_BWD", "0") == "1" and reserve == 0
+        self._bwd_ctas = int(os.environ.get("HVD_BWD_CTAS", 148))
+        self._bwd_nw = int(os.environ.get("HVD_BWD_NW", 0))          # CTAs that reduce wgrad strips first (0 = default)
+        self._bwd_t1 = int(os.environ.get("HVD_BWD_T1", -1))         # dgrad tiles those CTAs still take (-1 = default)
         if hasattr(opt, "set_bucket_cuts") and self.fused is not None:
             opt.set_bucket_cuts([f"{self.names['f1']}/kernel"] if self._bucket_mode == "overlap" else [])
             self.fused = opt._fused
@@ -209,7 +218,7 @@ class MnistEngine:
         self.use_graph = os.environ.get("HVD_NO_GRAPH", "0") != "1" and self.fused is not None
         if self.fused is not None:
             opt._defer_push = True           # hyper-parameter rows are written at step start (see _run_step)
-        self.launches_per_step = 8 + (len(self.fused.buckets) if self.fused is not None else 0)
+        self.launches_per_step = (7 if self._fused_bwd else 8) + (len(self.fused.buckets) if self.fused is not None else 0)
 
     # ------------------------------------------------------------------ helpers
     _GUARD_BYTES = 4096
@@ -330,22 +339,32 @@ class MnistEngine:
         lib, fused = self.lib, self.fused
         main = torch.cuda.current_stream(self.dev)
         s = self._s()
-        self._ev_dx.record(main)
-        self.side2.wait_event(self._ev_dx)
-        with torch.cuda.stream(self.side2):
-            if "wgrad" not in self._SKIP:
-                # (CTA 0 of this kernel also writes the step's loss/accuracy into the pinned host ring)
-                self._chk(lib.hvd_conv2_wgrad_ex(self.a1.data_ptr(), self.dy2.data_ptr(),
-                                                 self._g("c2", "kernel", which).data_ptr(),
-                                                 self._g("c2", "bias", which).data_ptr(), B, self._wgrad_ctas,
-                                                 self.side2.cuda_stream, self.state.data_ptr(), self._ring_ptr), "conv2_wgrad")
-        # conv2 dgrad with conv1's ReLU backward AND conv1's weight/bias gradient fused in (da1 never
-        # touches global memory)
-        if "dgrad" not in self._SKIP:
-            self._chk(lib.hvd_conv2_dgrad(self.dy2.data_ptr(), self._p("c2", "kernel").data_ptr(), self.a1.data_ptr(),
-                                          None, B, self._dgrad_ctas, s, self.x_bufs[which].data_ptr(),
-                                          self._g("c1", "kernel", which).data_ptr(),
-                                          self._g("c1", "bias", which).data_ptr()), "conv2_dgrad")
+        if self._fused_bwd and not ({"dgrad", "wgrad"} & self._SKIP):
+            # ONE kernel: every CTA does its share of conv2 wgrad strips, then its share of dgrad tiles (with
+            # conv1's ReLU backward and weight/bias gradient fused in); CTA 0 also publishes the step's
+            # loss/accuracy into the pinned host ring.  dense1's dW (side2) only has to be done before the update.
+            self._chk(lib.hvd_conv2_bwd(self.dy2.data_ptr(), self._p("c2", "kernel").data_ptr(), self.a1.data_ptr(),
+                                        self.x_bufs[which].data_ptr(), self._g("c2", "kernel", which).data_ptr(),
+                                        self._g("c2", "bias", which).data_ptr(), self._g("c1", "kernel", which).data_ptr(),
+                                        self._g("c1", "bias", which).data_ptr(), B, self._bwd_ctas, s,
+                                        self.state.data_ptr(), self._ring_ptr, self._bwd_nw, self._bwd_t1), "conv2_bwd")
+        else:
+            self._ev_dx.record(main)
+            self.side2.wait_event(self._ev_dx)
+            with torch.cuda.stream(self.side2):
+                if "wgrad" not in self._SKIP:
+                    # (CTA 0 of this kernel also writes the step's loss/accuracy into the pinned host ring)
+                    self._chk(lib.hvd_conv2_wgrad_ex(self.a1.data_ptr(), self.dy2.data_ptr(),
+                                                     self._g("c2", "kernel", which).data_ptr(),
+                                                     self._g("c2", "bias", which).data_ptr(), B, self._wgrad_ctas,
+                                                     self.side2.cuda_stream, self.state.data_ptr(), self._ring_ptr), "conv2_wgrad")
+            # conv2 dgrad with conv1's ReLU backward AND conv1's weight/bias gradient fused in (da1 never
+            # touches global memory)
+            if "dgrad" not in self._SKIP:
+                self._chk(lib.hvd_conv2_dgrad(self.dy2.data_ptr(), self._p("c2", "kernel").data_ptr(), self.a1.data_ptr(),
+                                              None, B, self._dgrad_ctas, s, self.x_bufs[which].data_ptr(),
+                                              self._g("c1", "kernel", which).data_ptr(),
+                                              self._g("c1", "bias", which).data_ptr()), "conv2_dgrad")
         main.wait_stream(self.side2)
         if fused is not None and "b1" not in self._SKIP:
             for i in range(1 if self._bucket_mode == "overlap" else 0, len(fused.buckets)):

@@ -143,6 +143,12 @@ int hvd_conv2_wgrad(const float* a1, const float* dy2, float* g_w, float* g_b, i
  * host buffer of 16 x 4 floats, as one 16-byte store.  The host polls the step word. */
 int hvd_conv2_wgrad_ex(const float* a1, const float* dy2, float* g_w, float* g_b, int B, int ctas, void* stream,
                        const void* step_state, float* host_ring);
+/* hvd_conv2_wgrad_ex followed by hvd_conv2_dgrad (with the fused conv1 gradients, no da1 output) as ONE kernel:
+ * the first `wgrad_ctas` CTAs reduce the wgrad strips and then take `wgrad_cta_tiles` dgrad tiles each, the other
+ * CTAs split the remaining dgrad tiles.  All four gradient outputs are accumulated (zero them first). */
+int hvd_conv2_bwd(const float* dy2, const float* w2, const float* a1, const float* x, float* g_w2, float* g_b2,
+                  float* g_w1, float* g_b1, int B, int ctas, void* stream, const void* step_state, float* host_ring,
+                  int wgrad_ctas /* <= 0: default */, int wgrad_cta_tiles /* < 0: default */);
 int hvd_conv1_wgrad(const float* x, const float* da1, float* g_w, float* g_b, int B, void* stream);
 int hvd_colsum64(const float* m, float* out, long long rows, void* stream);
 

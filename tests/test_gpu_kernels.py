@@ -212,6 +212,15 @@ def test_conv2_dgrad_and_wgrad_and_conv1_wgrad():
         gb2 = torch.ones(64, device="cuda")
         assert lib.hvd_conv2_wgrad(a1r.data_ptr(), dy2.data_ptr(), gw2.data_ptr(), gb2.data_ptr(), B, ctas, _s()) == 0
         assert _rel(gw2 - 1.0, dw_ref) < 3e-3 and _rel(gb2 - 1.0, dy2.double().sum(dim=(0, 1, 2))) < 1e-3
+    # wgrad + dgrad (+ conv1 wgrad) as one kernel
+    lib.hvd_conv2_bwd.argtypes = [ctypes.c_void_p] * 8 + [ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 3 + [ctypes.c_int] * 2
+    for ctas, nw, t1 in ((0, 0, -1), (37, 5, 0), (148, 64, 3), (2, 1, 7)):
+        gw4, gb4 = torch.zeros(3, 3, 32, 64, device="cuda"), torch.zeros(64, device="cuda")
+        f1w4, f1b4 = torch.zeros(3, 3, 1, 32, device="cuda"), torch.zeros(32, device="cuda")
+        assert lib.hvd_conv2_bwd(dy2.data_ptr(), w2.data_ptr(), a1r.data_ptr(), x.data_ptr(), gw4.data_ptr(), gb4.data_ptr(),
+                                 f1w4.data_ptr(), f1b4.data_ptr(), B, ctas, _s(), None, None, nw, t1) == 0
+        assert _rel(gw4, dw_ref) < 3e-3 and _rel(gb4, dy2.double().sum(dim=(0, 1, 2))) < 1e-3
+        assert _rel(f1w4, f1w) < 1e-3 and _rel(f1b4, f1b) < 1e-3
     gb3 = torch.zeros(64, device="cuda")
     lib.hvd_colsum64.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p]
     assert lib.hvd_colsum64(dy2.data_ptr(), gb3.data_ptr(), B * 576, _s()) == 0
