@@ -161,7 +161,6 @@ class MnistEngine:
         self.probs = self._alloc("probs", (B, 10), torch.float32)
         self._pin_x = torch.empty(B, 28 * 28, dtype=torch.float32).pin_memory()
         self._pin_y = torch.empty(B, dtype=torch.int64).pin_memory()
-        self._pin_out = torch.zeros(2, dtype=torch.float32).pin_memory()
         self._pin_x_np, self._pin_y_np = self._pin_x.numpy(), self._pin_y.numpy()
         self._ring_np = self._pin_ring.numpy()
         self._ring_ptr = self._pin_ring.data_ptr()
@@ -174,16 +173,13 @@ class MnistEngine:
         rank = basics.rank() if basics.is_initialized() else 0
         self.state[5] = (seed * 2654435761 + 97 * rank + 1) & 0x7FFFFFFF     # per-rank dropout masks
         self.state_f = self.state.view(torch.float32)
-        self._result_ptr = self.state.data_ptr() + 12          # (last_loss, last_correct) = words 3, 4
         self._graphs = {}
-        self._host_step = 0
         self._parity = 0
         self.side = torch.cuda.Stream(device=dev)
         self.side2 = torch.cuda.Stream(device=dev)
         self._ev_fork = torch.cuda.Event()
         self._ev_dx = torch.cuda.Event()
         self._ev_b = torch.cuda.Event()
-        self._ev_b0 = torch.cuda.Event()
         opt = model.optimizer
         self.fused = getattr(opt, "_fused", None)
         # HVD_BUCKET_MODE=tail: ONE bucket reduced + updated after the whole backward.
@@ -497,7 +493,6 @@ class MnistEngine:
             self._parity ^= 1 if self.m.arena.n_grad_bufs == 2 else 0
             if self._debug:
                 opt._debug_after_step(self.m.arena, which)
-        self._host_step += 1
         self._train_steps += 1
         nvtx.pop()
 
