@@ -12,6 +12,7 @@ user asked for per-batch output (``update_freq='batch'`` does, as in the referen
 """
 from __future__ import annotations
 
+import collections
 import os
 import sys
 import time
@@ -168,6 +169,7 @@ class TensorBoard(Callback):
         self._writer = None
         self._val_writer = None
         self._step = 0
+        self._pending = collections.deque()      # (writer, tag, value, step) whose value is still on its way
 
     def _w(self):
         if self._writer is None:
@@ -190,7 +192,16 @@ class TensorBoard(Callback):
         writer.add_scalar(tag, v, step)
         metrics_sink.record(tag, v, step)
 
+    def _drain(self, force: bool):
+        """Write the per-batch scalars whose values have arrived (all of them when ``force``), in order.
+        With an asynchronous backend a batch's values land while the next batch is already running, so they
+        are written one batch late instead of stalling the training loop on every step."""
+        from .utils import is_ready
+        while self._pending and (force or is_ready(self._pending[0][2])):
+            self._emit(*self._pending.popleft())
+
     def on_batch_end(self, batch, logs=None):
+        self._drain(False)
         self._step += 1
         if self.update_freq == "batch" or (isinstance(self.update_freq, int)
                                            and self._step % self.update_freq == 0):
@@ -198,9 +209,11 @@ class TensorBoard(Callback):
             for k, v in (logs or {}).items():
                 if k in ("batch", "size"):
                     continue
-                self._emit(w, "batch_" + k, v, self._step)
+                self._pending.append((w, "batch_" + k, v, self._step))
+            self._drain(False)
 
     def on_epoch_end(self, epoch, logs=None):
+        self._drain(True)
         for k, v in (logs or {}).items():
             if k.startswith("val_"):
                 self._emit(self._vw(), "epoch_" + k[4:], v, epoch)
@@ -214,6 +227,7 @@ class TensorBoard(Callback):
                 w.flush()
 
     def on_train_end(self, logs=None):
+        self._drain(True)
         for w in (self._writer, self._val_writer):
             if w is not None:
                 w.close()

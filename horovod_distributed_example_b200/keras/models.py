@@ -19,6 +19,7 @@ Both hand the arena's gradient slab to ``optimizer.apply_gradients``; with
 """
 from __future__ import annotations
 
+import collections
 import json
 import os
 import time
@@ -314,9 +315,14 @@ class Model:
         stream = None
         for epoch in range(initial_epoch, epochs):
             cl.on_epoch_begin(epoch, {})
-            # device-side running sums: no host sync per step
+            # No host sync per step.  A backend that publishes step results asynchronously
+            # (the fused engine: a pinned host ring) gives handles that are summed on the host as they land, a
+            # few steps behind the launches; other backends return device scalars summed on the device.
+            asynchronous = hasattr(be, "train_host_batch_async")
             loss_sum = torch.zeros((), dtype=torch.float64, device=self.device)
             acc_sum = torch.zeros((), dtype=torch.float64, device=self.device)
+            loss_h = acc_h = 0.0
+            pend = collections.deque()
             seen = 0
             if stream is None or not isinstance(x, Dataset):
                 stream = iter(it_factory())
@@ -327,24 +333,37 @@ class Model:
                     break
                 n = len(xb)
                 cl.on_batch_begin(step, {"batch": step, "size": n})
-                if hasattr(be, "train_host_lazy"):
-                    loss, acc = be.train_host_lazy(xb, yb)       # engine stages the batch itself (pipelined H2D)
+                if asynchronous:
+                    h = be.train_host_batch_async(xb, yb)        # engine stages the batch itself (pipelined H2D)
+                    pend.append((h, n))
+                    loss, acc = h.lazy()
+                    while pend and (len(pend) > 8 or pend[0][0].ready()):
+                        hh, nn = pend.popleft()
+                        lv, av = hh.result()
+                        loss_h += lv * nn
+                        acc_h += av * nn
                 else:
                     xd, yd = st(xb, torch.float32), st(yb)
                     st.next_step()
                     loss, acc = be.train_step(xd, yd)
-                loss_sum += loss.detach().to(torch.float64) * n
+                    loss_sum += loss.detach().to(torch.float64) * n
+                    if self._metric_accuracy:
+                        acc_sum += acc.detach().to(torch.float64) * n
                 seen += n
                 logs = {"batch": step, "size": n, "loss": loss}
                 if self._metric_accuracy:
-                    acc_sum += acc.detach().to(torch.float64) * n
                     logs["accuracy"] = acc
                 cl.on_batch_end(step, logs)
                 if self.stop_training:
                     break
-            elogs = {"loss": float(loss_sum) / max(seen, 1)}
+            while pend:
+                hh, nn = pend.popleft()
+                lv, av = hh.result()
+                loss_h += lv * nn
+                acc_h += av * nn
+            elogs = {"loss": (loss_h if asynchronous else float(loss_sum)) / max(seen, 1)}
             if self._metric_accuracy:
-                elogs["accuracy"] = float(acc_sum) / max(seen, 1)
+                elogs["accuracy"] = (acc_h if asynchronous else float(acc_sum)) / max(seen, 1)
             if do_val:
                 vx, vy = validation_data[0], validation_data[1]
                 v = self.evaluate(vx, vy, batch_size=bs, verbose=0)

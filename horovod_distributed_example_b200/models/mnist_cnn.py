@@ -106,9 +106,14 @@ class _StepResult:
     page-locked host ring; ``result()`` polls that slot's step word - no copy node on the stream, no event."""
 
     def __init__(self, engine, seq):
-        self._e, self._seq = engine, seq
+        self._e, self._seq, self._val = engine, seq, None
+
+    def ready(self) -> bool:
+        return self._val is not None or int(self._e._ring_u32[self._seq & 15][2]) == self._seq
 
     def result(self):
+        if self._val is not None:
+            return self._val
         e, seq = self._e, self._seq
         slot_u, slot_f = e._ring_u32[seq & 15], e._ring_np[seq & 15]
         if int(slot_u[2]) != seq:
@@ -120,7 +125,13 @@ class _StepResult:
                     if e.fused is not None:
                         e.fused.ctx.check_error()          # a stalled peer is the usual reason: name it
                     raise RuntimeError(f"step {seq} did not finish within {e._result_timeout:.0f} s")
-        return float(slot_f[0]), float(slot_f[1])
+        self._val = (float(slot_f[0]), float(slot_f[1]))
+        return self._val
+
+    def lazy(self):
+        """(loss, accuracy) as ``keras.utils.LazyScalar`` objects for per-batch callback logs."""
+        from ..keras.utils import LazyScalar
+        return (LazyScalar(lambda: self.result()[0], self.ready), LazyScalar(lambda: self.result()[1], self.ready))
 
 
 class MnistEngine:
@@ -144,6 +155,8 @@ class MnistEngine:
         self.y_bufs = [torch.zeros(B, dtype=torch.int64, device=dev) for _ in range(2)]
         self.x_in, self.y_in = self.x_bufs[0], self.y_bufs[0]     # parity 0 (also used by eval / predict)
         self.copy_stream = torch.cuda.Stream(device=dev)
+        self._dev_index = dev.index if dev.index is not None else torch.cuda.current_device()
+        self._main_raw, self._main_obj = None, None
         self._ev_in = [torch.cuda.Event(), torch.cuda.Event()]        # H2D of parity p finished
         self._ev_done = [torch.cuda.Event(), torch.cuda.Event()]      # step that read parity p finished
         self._pin_ring = torch.zeros(16, 4, dtype=torch.float32).pin_memory()      # written by the head kernel
@@ -251,7 +264,17 @@ class MnistEngine:
     _SKIP = set(filter(None, os.environ.get("HVD_ABLATE", "").split(",")))   # profiling only: drop kernels from the step
 
     def _s(self):
-        return torch.cuda.current_stream(self.dev).cuda_stream
+        return torch._C._cuda_getCurrentRawStream(self._dev_index)
+
+    def _main(self):
+        """The current stream as a Stream object.  ``torch.cuda.current_stream`` costs several microseconds of
+        Python per call and the per-step path needs it twice, so the object is cached and only re-created
+        when the raw handle of the current stream has changed."""
+        raw = torch._C._cuda_getCurrentRawStream(self._dev_index)
+        if raw != self._main_raw:
+            self._main_obj = torch.cuda.current_stream(self.dev)
+            self._main_raw = raw
+        return self._main_obj
 
     def _p(self, key, short):
         return self.m.arena.param(f"{self.names[key]}/{short}")
@@ -393,7 +416,7 @@ class MnistEngine:
         if xa.size != B * 784:
             raise ValueError(f"expected {B} x 28 x 28 x 1 inputs, got shape {tuple(xa.shape)}")
         w = self._which()
-        main = torch.cuda.current_stream(self.dev)
+        main = self._main()
         cs = self.copy_stream
         xp, yp = xa.ctypes.data, ya.ctypes.data
         if not (self._pinned(xa, xp) and self._pinned(ya, yp)):
@@ -468,7 +491,7 @@ class MnistEngine:
             if self._fault is not None and _fault_skip():   # HVD_FAULT_INJECT=rank:step: this rank skips the step
                 return
         which = self._which()
-        main = torch.cuda.current_stream(self.dev)
+        main = self._main()
         nvtx.push("hvd.step")
         if fused is not None and (opt._hyper_dirty > 0 or opt.kind == 3 or getattr(opt, "decay", 0.0) > 0.0):
             # this step's row of the hyper-parameter block (LR changed by a callback, Adam's lr_t, LR decay);

@@ -348,3 +348,32 @@ def test_async_host_steps_match_blocking_steps():
     for wa, wb in zip(a.get_weights(), b.get_weights()):
         np.testing.assert_allclose(wa, wb, rtol=0, atol=5e-3)
     hvd.shutdown()
+
+
+@pytest.mark.gpu
+def test_fit_per_batch_logs_arrive_without_a_sync(tmp_path):
+    """fit() on the fused engine hands callbacks LazyScalars: TensorBoard(update_freq='batch') still records every
+    batch exactly once, in order, and the epoch loss equals the sample-weighted mean of those batch losses."""
+    _lib()
+    hvd, build = _models(0.25, 0.5, "adadelta")
+    from horovod_distributed_example_b200 import keras
+    from horovod_distributed_example_b200.utils import tfevents
+    (x, y), _ = keras.datasets.synthetic_mnist(2048 + 40, 16)
+    x = (x[..., None] / 255.0).astype(np.float32)
+    m = build()
+    seen = []
+    cbs = [keras.callbacks.TensorBoard(log_dir=str(tmp_path), update_freq="batch"),
+           keras.callbacks.LambdaCallback(on_batch_end=lambda b, logs: seen.append(type(logs["loss"]).__name__))]
+    h = m.fit(x, y, batch_size=128, epochs=2, verbose=0, callbacks=cbs)
+    assert type(m._backend).__name__ == "MnistEngine" and set(seen) == {"LazyScalar"}
+    ev = tfevents.read_scalars(str(next((tmp_path / "train").iterdir())))
+    bl = [(s, v) for t, s, v in ev if t == "batch_loss"]
+    assert [s for s, _ in bl] == list(range(1, 35))                 # 17 steps x 2 epochs, each once, in order
+    sizes = [128] * 16 + [40]
+    for ep in range(2):
+        vals = [v for _, v in bl[17 * ep:17 * (ep + 1)]]
+        assert np.isfinite(vals).all()
+        want = sum(v * n for v, n in zip(vals, sizes)) / sum(sizes)
+        assert abs(h.history["loss"][ep] - want) < 1e-5 * max(1.0, abs(want))
+    assert h.history["loss"][1] < h.history["loss"][0]
+    hvd.shutdown()

@@ -188,3 +188,47 @@ def test_debug_poison_marks_consumed_gradients(hvd_single, monkeypatch):
         assert torch.isfinite(m.arena.params).all()
     finally:
         hvd.basics.state().config.debug_poison = False
+
+
+def test_lazy_scalars_defer_tensorboard_batch_writes(tmp_path):
+    """Per-batch logs may be LazyScalars (asynchronous backend): TensorBoard must not block on a value that has
+    not arrived, must write every batch scalar exactly once, in order, and flush the rest at epoch end."""
+    from horovod_distributed_example_b200.keras.utils import LazyScalar, is_ready
+    arrived = set()
+    forced = []
+
+    def lazy(i):
+        def resolve():
+            if i not in arrived:
+                forced.append(i)                      # somebody blocked on a value that was not there yet
+            return float(i)
+        return LazyScalar(resolve, lambda: i in arrived)
+
+    tb = keras.callbacks.TensorBoard(log_dir=str(tmp_path), update_freq="batch")
+    tb.set_params({"steps": 4})
+    for b in range(4):
+        if b > 0:
+            arrived.add(b - 1)                        # the previous batch's result lands while this one runs
+        tb.on_batch_end(b, {"batch": b, "size": 8, "loss": lazy(b)})
+        assert len(tb._pending) == 1                  # only the newest batch is still on its way
+    assert forced == []
+    tb.on_epoch_end(0, {"loss": 1.5})                 # forces the last one
+    assert forced == [3] and not tb._pending
+    tb.on_train_end()
+    ev = [(st, val) for tag, st, val in tfevents.read_scalars(str(next((tmp_path / "train").iterdir()))) if tag == "batch_loss"]
+    assert ev == [(1, 0.0), (2, 1.0), (3, 2.0), (4, 3.0)]
+    v = lazy(7)
+    assert not is_ready(v) and is_ready(3.0) and f"{v:.1f}" == "7.0" and v.ready()
+
+
+def test_array_batcher_gathers_every_row_once():
+    x = np.arange(1000 * 3, dtype=np.float32).reshape(1000, 3)
+    y = np.arange(1000)
+    for shuffle in (True, False):
+        from horovod_distributed_example_b200.keras.data import ArrayBatcher
+        b = ArrayBatcher([x, y], 128, shuffle, seed=0)
+        seen = []
+        for xb, yb in b.epoch():
+            assert (xb[:, 0] == yb * 3).all()
+            seen.append(yb.copy())                    # a ring slot is reused RING batches later
+        assert b.steps == 8 and sorted(np.concatenate(seen).tolist()) == list(range(1000))
