@@ -13,6 +13,7 @@ trainer's per-step H2D copy is asynchronous.
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, Iterator, Optional, Sequence, Tuple
 
 import numpy as np
@@ -173,12 +174,19 @@ class ArrayBatcher:
 
     With CUDA available the rows of a batch are gathered straight into a ring of page-locked buffers
     (``np.take(..., out=...)``): no per-batch allocation, and the trainer's host->device copy of the batch is
-    truly asynchronous.  A yielded batch stays valid for ``RING - 1`` further batches - ``fit`` never runs
-    more than 8 steps ahead of the device."""
+    truly asynchronous.  With ``prefetch=True`` (or ``HVD_PREFETCH_THREAD=1``) the gather (~50 us for a 128 x 784
+    float batch out of 60,000 shuffled rows) runs on a thread, up to ``AHEAD`` batches in front of the consumer;
+    ``np.take`` releases the GIL, so it can overlap the training thread's launch work.
 
-    RING = 16
+    A yielded batch stays valid until ``RING - AHEAD - 1`` further batches have been taken - ``fit`` never runs
+    more than 8 steps ahead of the device, so the copy of a batch has left host memory long before its slot
+    is reused."""
 
-    def __init__(self, arrays: Sequence[np.ndarray], batch_size: int, shuffle: bool, seed=None, pinned=None):
+    RING = 24
+    AHEAD = 6
+
+    def __init__(self, arrays: Sequence[np.ndarray], batch_size: int, shuffle: bool, seed=None, pinned=None,
+                 prefetch=None):
         self.arrays = [np.ascontiguousarray(a) for a in arrays]
         self.n = len(self.arrays[0])
         self.batch_size = int(batch_size)
@@ -196,6 +204,11 @@ class ArrayBatcher:
                 self._ring = [t.numpy() for t in self._keep]
             except Exception:                     # no CUDA runtime / unsupported dtype: plain batches
                 self._ring = None
+        if self._ring is None and prefetch:       # (tests) the threaded path without page-locked memory
+            self._ring = [np.empty((self.RING, self.batch_size) + a.shape[1:], dtype=a.dtype) for a in self.arrays]
+        if prefetch is None:
+            prefetch = os.environ.get("HVD_PREFETCH_THREAD", "0") == "1"
+        self.prefetch = bool(prefetch) and self._ring is not None
 
     @property
     def steps(self) -> int:
@@ -212,16 +225,60 @@ class ArrayBatcher:
             out.append(dst)
         return tuple(out)
 
-    def epoch(self):
+    def _index_batches(self):
         order = self.rng.permutation(self.n) if self.shuffle else None
         for s in range(0, self.n, self.batch_size):
             if order is None:
-                if self._ring is None:
-                    yield tuple(a[s:s + self.batch_size] for a in self.arrays)
-                else:
-                    yield self._gather(np.arange(s, min(s + self.batch_size, self.n)))
+                yield None if self._ring is None else np.arange(s, min(s + self.batch_size, self.n)), s
             else:
-                yield self._gather(order[s:s + self.batch_size])
+                yield order[s:s + self.batch_size], s
+
+    def _take(self, idx, s):
+        if idx is None:                           # unshuffled, no ring: plain views of the source arrays
+            return tuple(a[s:s + self.batch_size] for a in self.arrays)
+        return self._gather(idx)
+
+    def epoch(self):
+        if not self.prefetch:
+            for idx, s in self._index_batches():
+                yield self._take(idx, s)
+            return
+        import queue
+        import threading
+        q: "queue.Queue" = queue.Queue(maxsize=self.AHEAD)
+        stop = threading.Event()
+
+        def put(item) -> bool:
+            while not stop.is_set():
+                try:
+                    q.put(item, timeout=0.05)
+                    return True
+                except queue.Full:
+                    pass
+            return False
+
+        def produce():
+            try:
+                for idx, s in self._index_batches():
+                    if not put(self._take(idx, s)):
+                        return
+                put(None)
+            except BaseException as e:            # surface producer errors in the consumer
+                put(e)
+
+        t = threading.Thread(target=produce, name="hvd-batch-prefetch", daemon=True)
+        t.start()
+        try:
+            while True:
+                item = q.get()
+                if item is None:
+                    break
+                if isinstance(item, BaseException):
+                    raise item
+                yield item
+        finally:                                  # also runs when the consumer abandons the epoch early
+            stop.set()
+            t.join()
 
 
 def _cuda_available() -> bool:

@@ -232,3 +232,17 @@ def test_array_batcher_gathers_every_row_once():
             assert (xb[:, 0] == yb * 3).all()
             seen.append(yb.copy())                    # a ring slot is reused RING batches later
         assert b.steps == 8 and sorted(np.concatenate(seen).tolist()) == list(range(1000))
+
+
+def test_array_batcher_prefetch_thread_matches_inline_order():
+    import threading
+    from horovod_distributed_example_b200.keras.data import ArrayBatcher
+    x = np.arange(5000 * 2, dtype=np.float32).reshape(5000, 2)
+    y = np.arange(5000)
+    a = [yb.copy() for _, yb in ArrayBatcher([x, y], 64, True, seed=3, pinned=False, prefetch=False).epoch()]
+    b = [yb.copy() for _, yb in ArrayBatcher([x, y], 64, True, seed=3, pinned=False, prefetch=True).epoch()]
+    assert len(a) == len(b) == 79 and all((p == q).all() for p, q in zip(a, b))
+    g = ArrayBatcher([x, y], 64, True, seed=3, pinned=False, prefetch=True).epoch()
+    next(g)
+    g.close()                                         # abandoning an epoch stops and joins the thread
+    assert not [t for t in threading.enumerate() if t.name == "hvd-batch-prefetch"]
