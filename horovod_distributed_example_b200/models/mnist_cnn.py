@@ -310,18 +310,23 @@ class MnistEngine:
             nb = ar.n - first_conv
             za, zb = g.data_ptr(), g.data_ptr() + 4 * first_conv
         xin = self.x_bufs[which or 0]
-        if "conv1_fwd" not in self._SKIP: self._chk(lib.hvd_conv1_fwd(xin.data_ptr(), self._p("c1", "kernel").data_ptr(),
-                                    self._p("c1", "bias").data_ptr(), self.a1.data_ptr(), B, za, na, zb, nb,
-                                    self.state.data_ptr(), int(which is not None), s), "conv1_fwd")
-        if "fprop" not in self._SKIP: self._chk(lib.hvd_conv2_fprop(self.a1.data_ptr(), self._p("c2", "kernel").data_ptr(),
-                                      self._p("c2", "bias").data_ptr(), self.p2.data_ptr(), self.mask2.data_ptr(),
-                                      self.state.data_ptr(), B, int(training), self.keep1, 0, s), "conv2_fprop")
+        if "conv1_fwd" not in self._SKIP:
+            self._chk(lib.hvd_conv1_fwd(xin.data_ptr(), self._p("c1", "kernel").data_ptr(),
+                                        self._p("c1", "bias").data_ptr(), self.a1.data_ptr(), B, za, na, zb, nb,
+                                        self.state.data_ptr(), int(which is not None), s), "conv1_fwd")
+        if "fprop" not in self._SKIP:
+            self._chk(lib.hvd_conv2_fprop(self.a1.data_ptr(), self._p("c2", "kernel").data_ptr(),
+                                          self._p("c2", "bias").data_ptr(), self.p2.data_ptr(), self.mask2.data_ptr(),
+                                          self.state.data_ptr(), B, int(training), self.keep1, 0, s), "conv2_fprop")
 
     def _head(self, B: int, training: bool, backward: bool, which: int = 0, probs: bool = False):
         gp = (lambda k, sh: self._g(k, sh, which).data_ptr()) if backward else (lambda k, sh: None)
-        if "head" not in self._SKIP: self._chk(self.lib.hvd_head(self.h_pre.data_ptr(), self._p("f1", "bias").data_ptr(),
+        if "head" in self._SKIP:
+            return
+        labels = self.y_bufs[which if backward else 0]
+        self._chk(self.lib.hvd_head(self.h_pre.data_ptr(), self._p("f1", "bias").data_ptr(),
                                     self._p("f2", "kernel").data_ptr(), self._p("f2", "bias").data_ptr(),
-                                    self.y_bufs[which if backward else 0].data_ptr(), self.dh_pre.data_ptr(), gp("f2", "kernel"),
+                                    labels.data_ptr(), self.dh_pre.data_ptr(), gp("f2", "kernel"),
                                     gp("f2", "bias"), gp("f1", "bias"),
                                     self.probs.data_ptr() if probs else None, self.state.data_ptr(), B,
                                     int(training), int(backward), self.keep2, self._s()), "head")

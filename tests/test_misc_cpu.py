@@ -246,3 +246,18 @@ def test_array_batcher_prefetch_thread_matches_inline_order():
     next(g)
     g.close()                                         # abandoning an epoch stops and joins the thread
     assert not [t for t in threading.enumerate() if t.name == "hvd-batch-prefetch"]
+
+
+def test_variant_pick_and_cta_defaults():
+    """Variant table: small messages one-shot, large ones NVLS where available (two-shot otherwise); a single
+    GPU gets two update CTAs per SM for a large bucket; NVLS never exceeds its measured 32-CTA optimum."""
+    from horovod_distributed_example_b200.parallel import variants as V
+    assert V.default_ctas(4_800_000, V.TWOSHOT, 1) == 293            # ceil(4.8 MB / 16 KB), below the 296 cap
+    assert V.default_ctas(64 << 20, V.TWOSHOT, 1) == 296
+    assert V.default_ctas(1024, V.ONESHOT, 1) == 1
+    assert V.default_ctas(64 << 20, V.NVLS, 8) == 32 and V.default_ctas(64 << 20, V.TWOSHOT, 8) == 148
+    v_small, _ = V.pick(1024, 8, True)
+    v_big, c_big = V.pick(64 << 20, 8, True)
+    v_big_no_mc, _ = V.pick(64 << 20, 8, False)
+    assert v_small == V.ONESHOT and v_big == V.NVLS and v_big_no_mc == V.TWOSHOT and c_big <= 32
+    assert V.pick(1 << 20, 8, True, forced="twoshot", forced_ctas=17) == (V.TWOSHOT, 17)
