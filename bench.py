@@ -32,8 +32,8 @@ BATCH = 128
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch_nccl"])
     ap.add_argument("--optimizer", default="adadelta", choices=["adadelta", "adam"])
     ap.add_argument("--no-e2e", action="store_true")
@@ -41,17 +41,49 @@ def parse():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    """SM clock and throttle reasons DURING the timed region.
+
+    The timed region of this benchmark is tens of milliseconds, shorter than nvidia-smi's fastest loop, so the
+    primary sampler is an NVML polling thread (one sample every 5 ms, started right before the first timed step
+    and stopped right after the last).  If NVML cannot be loaded it falls back to `nvidia-smi -lms 100`, whose
+    samples then mostly fall just after the region."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    PERIOD = 0.005
 
     def __init__(self, gpu_index: int):
         self.idx = gpu_index
         self.proc = None
         self.lines = []
+        self.nvml = None
+        self.samples = []           # (sm_mhz, reasons bitmask)
+        self.max_mhz = None
+        self._stop = threading.Event()
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            import torch
+            pr = torch.cuda.get_device_properties(self.idx)
+            bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+        return pynvml, h
 
     def start(self):
+        try:
+            self.nvml, self.h = self._nvml_handle()
+            self.max_mhz = float(self.nvml.nvmlDeviceGetMaxClockInfo(self.h, self.nvml.NVML_CLOCK_SM))
+            self._sample()           # make sure the calls work before committing to this path
+            self.thr = threading.Thread(target=self._poll, daemon=True)
+            self.thr.start()
+            return
+        except Exception:
+            self.nvml = None
+            self.samples = []
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
@@ -61,11 +93,40 @@ class ClockSampler:
         except OSError:
             self.proc = None
 
+    def _sample(self):
+        n = self.nvml
+        self.samples.append((float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)),
+                             int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))))
+
+    def _poll(self):
+        while not self._stop.wait(self.PERIOD):
+            try:
+                self._sample()
+            except Exception:
+                return
+
     def _read(self):
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self._stop.set()
+            self.thr.join(1.0)
+            n = self.nvml
+            try:
+                self._sample()       # one more right at the end of the region
+            except Exception:
+                pass
+            bits = {"hw_slowdown": n.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": n.nvmlClocksEventReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": n.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": n.nvmlClocksEventReasonSwPowerCap,
+                    "hw_power_brake_slowdown": n.nvmlClocksEventReasonHwPowerBrakeSlowdown}
+            sm = sorted(s for s, _ in self.samples[1:]) or sorted(s for s, _ in self.samples)   # [0] predates the region
+            seen = 0
+            for _, r in self.samples[1:]:
+                seen |= r
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz,
+                    "reasons": sorted(k for k, b in bits.items() if seen & b), "samples": len(sm), "source": "nvml, 5 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -90,7 +151,7 @@ class ClockSampler:
                     reasons.add(nm)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
 def reference_arm(args):
