@@ -259,10 +259,16 @@ def _models(rate1, rate2, opt_name):
     return hvd, build
 
 
-@pytest.mark.parametrize("opt_name", ["adadelta", "adam"])
-def test_engine_matches_torch_oracle_without_dropout(opt_name, monkeypatch):
-    """Whole fused step (CUDA graph, fused update) vs the torch-autograd oracle, dropout rate 0."""
+@pytest.mark.parametrize("opt_name,env", [("adadelta", {}), ("adam", {}),
+                                          ("adadelta", {"HVD_BUCKET_MODE": "overlap"}),        # bucket 0 on a side stream
+                                          ("adam", {"HVD_FUSED_BWD": "1"}),                     # wgrad + dgrad as one kernel
+                                          ("adadelta", {"HVD_BUCKET_MODE": "overlap", "HVD_RESERVE_SMS": "0"})])
+def test_engine_matches_torch_oracle_without_dropout(opt_name, env, monkeypatch):
+    """Whole fused step (CUDA graph, fused update) vs the torch-autograd oracle, dropout rate 0 - in the default
+    configuration and in the selectable step shapes."""
     _lib()
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
     hvd, build = _models(0.0, 0.0, opt_name)
     rng = np.random.default_rng(0)
     X = rng.random((3, B, 28, 28, 1), dtype=np.float32)
