@@ -24,8 +24,11 @@
 //        the three dY2 rows that pair with it, both channel halves (N = 192): one MMA per a1 row does all
 //        nine taps.  The bias gradient (column sums of dY2) is summed from the smem tile by the otherwise
 //        idle epilogue warps while the tensor core works.  Details at namespace wg.
-//        Each CTA reduces a range of 8-column image strips (split-K) and adds its 288x64 result into the
-//        arena with red.add.v4.
+//        Each CTA reduces its share of the 8-column image strips (dealt round-robin: split-K) and adds its
+//        288x64 result into the arena with red.add.v4.
+//
+// Both are device functions (dg::body, wg::body): each has its own kernel, and conv2_bwd_kernel runs them back to
+// back in one launch with an unequal strip/tile split (hvd_conv2_bwd).
 #include "mnist_common.cuh"
 #include "tc_common.cuh"
 
