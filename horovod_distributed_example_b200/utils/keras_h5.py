@@ -125,7 +125,9 @@ def load_weights_into(model, path: str) -> None:
         be.weights_changed()
 
 
-def load_model(path: str, compile: bool = True):
+def load_model(path: str, compile: bool = True, wrap_optimizer=None):
+    """``wrap_optimizer``: optional callable applied to the deserialized optimizer before ``compile`` (``hvd.load_model``
+    passes ``DistributedOptimizer``); the saved optimizer state is loaded into the wrapped instance."""
     from ..keras import models as models_mod, optimizers as opt_mod
     with hdf5.Reader(path) as r:
         attrs = r.attr_names("/")
@@ -146,6 +148,8 @@ def load_model(path: str, compile: bool = True):
     load_weights_into(model, path)
     if compile and tc is not None:
         opt = opt_mod.deserialize(tc["optimizer_config"])
+        if wrap_optimizer is not None:
+            opt = wrap_optimizer(opt)
         model.compile(optimizer=opt, loss=tc["loss"], metrics=tc.get("metrics") or [])
         if has_opt and opt_arrays:
             with torch.no_grad():

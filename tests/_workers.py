@@ -152,6 +152,58 @@ def resume_from_checkpoint():
     print("OK")
 
 
+def hvd_load_model_and_optimizer_state():
+    """hvd.load_model on every rank (Horovod's resume recipe): the optimizer comes back wrapped, with its state;
+    broadcast_optimizer_state equalises keras-style and torch.optim optimizers; timeline control at run time."""
+    hvd.init()
+    r = hvd.rank()
+    out = os.environ["HVD_TEST_OUT"]
+    path = os.path.join(out, "ckpt.h5")
+    rng = np.random.default_rng(5)
+    x = rng.random((32, 28, 28, 1), dtype=np.float32)
+    y = rng.integers(0, 10, 32)
+    if r == 0:
+        m0 = _mnist_model(seed=1)
+        m0.compile(loss=keras.losses.SparseCategoricalCrossentropy(), optimizer=keras.optimizers.Adam(0.005))
+        for _ in range(2):
+            m0.train_on_batch(x, y)
+        m0.save(path)
+        ref_slots = [s.clone() for s in m0.arena.slots]
+    hvd.barrier()
+    hvd.start_timeline(os.path.join(out, "tl.json"))
+    m = hvd.load_model(path)                              # every rank
+    opt = m.optimizer
+    assert type(opt).__name__ == "Adam" and getattr(opt, "_hvd_distributed", False)
+    assert opt.iterations == 2 and abs(opt.lr - 0.005) < 1e-9      # Adam stores its iteration counter in the file
+    if r == 0:
+        for a, b in zip(m.arena.slots, ref_slots):
+            assert torch.equal(a, b)
+    # perturb rank 1's state, then equalise
+    if r == 1:
+        for s in m.arena.slots:
+            s.add_(1.0)
+        opt.iterations = 9
+    hvd.broadcast_optimizer_state(opt, 0, model=m)
+    st = hvd.allgather(torch.cat(list(m.arena.slots))[None])
+    assert torch.equal(st[0], st[1]) and opt.iterations == 2
+    m.train_on_batch(x, y)                                # continues training with averaged gradients
+    w = hvd.allgather(m.arena.params.clone()[None])
+    assert torch.equal(w[0], w[1])
+    # torch.optim flavour
+    lin = torch.nn.Linear(4, 3)
+    topt = torch.optim.Adam(lin.parameters(), lr=0.01 * (r + 1))
+    lin(torch.randn(5, 4) + r).sum().backward()
+    topt.step()
+    hvd.broadcast_parameters(lin.state_dict(), 0)
+    hvd.broadcast_optimizer_state(topt, 0)
+    ea = hvd.allgather(topt.state_dict()["state"][0]["exp_avg"].reshape(1, -1))
+    assert torch.equal(ea[0], ea[1]) and abs(topt.param_groups[0]["lr"] - 0.01) < 1e-12
+    hvd.stop_timeline()
+    if r == 0:
+        assert json.load(open(os.path.join(out, "tl.json")))   # a valid Chrome trace with the broadcasts in it
+    print("OK")
+
+
 def plan_mismatch():
     hvd.init()
     layers = [keras.layers.Flatten(), keras.layers.Dense(4 + hvd.rank())]

@@ -32,3 +32,7 @@ def test_bucket_plan_mismatch_detected():
 
 def test_resume_from_rank0_checkpoint_ws2(tmp_path):
     _ok(run_workers("resume_from_checkpoint", env={"HVD_TEST_OUT": str(tmp_path)}))
+
+
+def test_hvd_load_model_and_broadcast_optimizer_state_ws2(tmp_path):
+    _ok(run_workers("hvd_load_model_and_optimizer_state", env={"HVD_TEST_OUT": str(tmp_path)}))
