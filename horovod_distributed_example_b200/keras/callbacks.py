@@ -289,3 +289,84 @@ class ReduceLROnPlateau(Callback):
             opt = self.model.optimizer
             opt.lr = max(opt.lr * self.factor, self.min_lr)
             self.wait = 0
+
+
+class LearningRateScheduler(Callback):
+    """``schedule(epoch)`` or ``schedule(epoch, lr)`` -> new learning rate, applied at the start of every epoch
+    (the fused update kernels read the LR from a device block, so this costs one small upload, no re-capture)."""
+
+    def __init__(self, schedule, verbose=0):
+        super().__init__()
+        self.schedule, self.verbose = schedule, verbose
+
+    def on_epoch_begin(self, epoch, logs=None):
+        opt = self.model.optimizer
+        try:
+            lr = self.schedule(epoch, float(opt.lr))
+        except TypeError:
+            lr = self.schedule(epoch)
+        opt.lr = float(lr)
+        if self.verbose:
+            print(f"\nEpoch {epoch + 1:05d}: LearningRateScheduler setting learning rate to {opt.lr}.")
+
+    def on_epoch_end(self, epoch, logs=None):
+        if logs is not None:
+            logs["lr"] = float(self.model.optimizer.lr)
+
+
+class CSVLogger(Callback):
+    """One row of epoch metrics per epoch (``epoch,<sorted metric names>``)."""
+
+    def __init__(self, filename, separator=",", append=False):
+        super().__init__()
+        self.filename, self.sep, self.append = filename, separator, append
+        self._f = None
+        self._keys = None
+
+    def on_train_begin(self, logs=None):
+        new = not (self.append and os.path.exists(self.filename) and os.path.getsize(self.filename) > 0)
+        self._f = open(self.filename, "a" if self.append else "w")
+        self._header_due = new
+
+    def on_epoch_end(self, epoch, logs=None):
+        logs = logs or {}
+        if self._keys is None:
+            self._keys = sorted(logs)
+        if self._header_due:
+            self._f.write(self.sep.join(["epoch"] + self._keys) + "\n")
+            self._header_due = False
+        self._f.write(self.sep.join([str(epoch)] + [repr(float(logs[k])) if k in logs else "NA" for k in self._keys]) + "\n")
+        self._f.flush()
+
+    def on_train_end(self, logs=None):
+        if self._f is not None:
+            self._f.close()
+            self._f = None
+
+
+class TerminateOnNaN(Callback):
+    """Stop training when the loss of a batch is NaN or infinite.  Checks the batches whose results have already
+    arrived (no device sync is forced per step) and everything that is left at the end of the epoch."""
+
+    def __init__(self):
+        super().__init__()
+        self._pending = collections.deque()
+
+    def _check(self, force):
+        import math
+        from .utils import is_ready
+        while self._pending and (force or is_ready(self._pending[0][1])):
+            batch, v = self._pending.popleft()
+            v = float(v)
+            if math.isnan(v) or math.isinf(v):
+                print(f"Batch {batch}: Invalid loss, terminating training")
+                self.model.stop_training = True
+                self._pending.clear()
+
+    def on_batch_end(self, batch, logs=None):
+        if logs and "loss" in logs:
+            self._pending.append((batch, logs["loss"]))
+        self._check(False)
+
+    def on_epoch_end(self, epoch, logs=None):
+        self._check(True)

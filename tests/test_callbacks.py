@@ -96,3 +96,26 @@ def test_callback_order_lr_not_averaged(hvd_single):
         hvd.callbacks.LearningRateWarmupCallback(warmup_epochs=1),
         keras.callbacks.LambdaCallback(on_epoch_end=lambda e, logs: seen.update(logs))])
     assert set(seen) == {"loss", "accuracy", "lr"} and h.history["lr"] == [0.1, 0.1]
+
+
+def test_lr_scheduler_csv_logger_and_terminate_on_nan(tmp_path, hvd_single):
+    import numpy as np
+    from horovod_distributed_example_b200 import keras
+    rng = np.random.default_rng(0)
+    x = rng.normal(size=(96, 6)).astype(np.float32)
+    y = (x[:, 0] > 0).astype(np.int64)
+    m = keras.Sequential([keras.layers.Dense(8, activation="relu", input_shape=(6,)), keras.layers.Dense(2, activation="softmax")])
+    m.compile(loss="sparse_categorical_crossentropy", optimizer=keras.optimizers.SGD(0.1), metrics=["accuracy"])
+    csv = tmp_path / "log.csv"
+    h = m.fit(x, y, batch_size=32, epochs=3, verbose=0,
+              callbacks=[keras.callbacks.LearningRateScheduler(lambda e, lr: 0.1 * 0.5 ** e), keras.callbacks.CSVLogger(str(csv))])
+    assert h.history["lr"] == [0.1, 0.05, 0.025] and abs(m.optimizer.lr - 0.025) < 1e-12
+    rows = csv.read_text().strip().splitlines()
+    assert rows[0] == "epoch,accuracy,loss,lr" and len(rows) == 4 and rows[3].startswith("2,")
+    # a NaN loss stops training at the end of the epoch at the latest
+    m2 = keras.Sequential([keras.layers.Dense(2, activation="softmax", input_shape=(6,))])
+    m2.compile(loss="sparse_categorical_crossentropy", optimizer=keras.optimizers.SGD(0.1))
+    xb = x.copy()
+    xb[5, 2] = np.nan
+    h2 = m2.fit(xb, y, batch_size=32, epochs=5, verbose=0, shuffle=False, callbacks=[keras.callbacks.TerminateOnNaN()])
+    assert len(h2.history["loss"]) == 1 and m2.stop_training
