@@ -261,3 +261,23 @@ def test_variant_pick_and_cta_defaults():
     v_big_no_mc, _ = V.pick(64 << 20, 8, False)
     assert v_small == V.ONESHOT and v_big == V.NVLS and v_big_no_mc == V.TWOSHOT and c_big <= 32
     assert V.pick(1 << 20, 8, True, forced="twoshot", forced_ctas=17) == (V.TWOSHOT, 17)
+
+
+def test_launcher_horovodrun_style_flags(tmp_path):
+    """-H localhost:N sets the process count; tuning flags become the HVD_* variables hvd.init() reads; a remote host
+    is refused; --check-build reports the build."""
+    script = tmp_path / "f.py"
+    script.write_text("import os, json\nopen(os.environ['OUT'] + os.environ['HVD_RANK'], 'w').write(json.dumps("
+                      "{k: v for k, v in os.environ.items() if k.startswith('HVD_')}))\n")
+    base = [sys.executable, "-m", "horovod_distributed_example_b200.run"]
+    r = subprocess.run(base + ["-H", "localhost:2", "--fusion-threshold-mb", "2", "--timeline-filename", str(tmp_path / "t.json"),
+                               "--log-level", "INFO", "--cycle-time-ms", "3.5", "--allreduce-variant", "twoshot", "--gloo",
+                               "-x", f"OUT={tmp_path}/e", str(script)], cwd=ROOT, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    env = json.loads((tmp_path / "e1").read_text())
+    assert env["HVD_SIZE"] == "2" and env["HVD_FUSION_THRESHOLD"] == str(2 * 1024 * 1024)
+    assert env["HVD_LOG_LEVEL"] == "INFO" and env["HVD_ALLREDUCE_VARIANT"] == "twoshot" and env["HVD_TIMELINE"].endswith("t.json")
+    r = subprocess.run(base + ["-H", "some-other-host:4", str(script)], cwd=ROOT, capture_output=True, text=True)
+    assert r.returncode == 2 and "single-host" in r.stderr
+    r = subprocess.run(base + ["--check-build"], cwd=ROOT, capture_output=True, text=True)
+    assert r.returncode == 0 and "[X] Gloo" in r.stdout and "libhvd_core.so" in r.stdout
