@@ -281,3 +281,59 @@ def test_launcher_horovodrun_style_flags(tmp_path):
     assert r.returncode == 2 and "single-host" in r.stderr
     r = subprocess.run(base + ["--check-build"], cwd=ROOT, capture_output=True, text=True)
     assert r.returncode == 0 and "[X] Gloo" in r.stdout and "libhvd_core.so" in r.stdout
+
+
+def test_dataset_block_shuffle_matches_the_sequential_process():
+    """The vectorised shuffle buffer must equal element-by-element eviction for the same slot picks, including
+    slots picked several times inside one block."""
+    from horovod_distributed_example_b200.keras.data import _evict_block
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        B, m = int(rng.integers(1, 9)), int(rng.integers(1, 40))
+        buf = rng.integers(0, 1000, B)
+        blk = rng.integers(1000, 2000, m)
+        js = rng.integers(0, B, m)
+        ref_buf, ref_out = buf.copy(), []
+        for k in range(m):
+            ref_out.append(ref_buf[js[k]])
+            ref_buf[js[k]] = blk[k]
+        got_buf = buf.copy()
+        got = _evict_block(got_buf, blk, js)
+        assert got.tolist() == ref_out and got_buf.tolist() == ref_buf.tolist()
+
+
+def test_dataset_fast_path_and_fallback_agree_on_semantics():
+    x = np.arange(50)[:, None].astype(np.float32)
+    y = np.arange(50)
+    # fast path (repeat, shuffle, batch, take, map after batch)
+    ds = keras.Dataset.from_tensor_slices((x, y)).repeat(2).shuffle(8, seed=1).batch(16).take(5).map(lambda a, b: (a * 2, b))
+    assert ds._block_plan() is not None
+    bs = list(ds)
+    assert [len(b[1]) for b in bs] == [16] * 5 and all((b[0][:, 0] == 2 * b[1]).all() for b in bs)
+    full = np.concatenate([b[1] for b in keras.Dataset.from_tensor_slices((x, y)).repeat(2).shuffle(8, seed=1).batch(16)])
+    assert len(full) == 100 and np.bincount(full).tolist() == [2] * 50            # nothing lost or duplicated
+    assert [len(b[1]) for b in keras.Dataset.from_tensor_slices((x, y)).batch(16, drop_remainder=True)] == [16] * 3
+    # operator orders outside the pattern use the element-wise generators
+    slow = keras.Dataset.from_tensor_slices((x, y)).batch(5).repeat(2)
+    assert slow._block_plan() is None
+    early_map = keras.Dataset.from_tensor_slices((x, y)).map(lambda a, b: (a, b)).batch(10)
+    assert early_map._block_plan() is None and sum(len(b[1]) for b in early_map) == 50
+
+
+def test_dataset_batch_ring_reuses_slots_without_corrupting_recent_batches():
+    from horovod_distributed_example_b200.keras.data import _PinnedRing
+    x = np.arange(400 * 3, dtype=np.float32).reshape(400, 3)
+    y = np.arange(400)
+    ds = keras.Dataset.from_tensor_slices((x, y))
+    ds._force_ring = True
+    ds = ds.repeat(3).shuffle(50, seed=4).batch(32)
+    recent, total = [], []
+    for xb, yb in ds:
+        assert (xb[:, 0] == yb * 3).all()
+        total.append(yb.copy())
+        recent.append((xb, yb.copy()))
+        if len(recent) > _PinnedRing.RING - 1:
+            recent.pop(0)
+        for xr, yr in recent:                           # batches stay intact until their slot comes round again
+            assert (xr[:len(yr), 0] == yr * 3).all()
+    assert np.bincount(np.concatenate(total)).tolist() == [3] * 400
