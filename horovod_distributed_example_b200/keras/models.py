@@ -404,8 +404,9 @@ class Model:
         if first_shape is not None:
             self._ensure_built(first_shape)
         st = self._stager()
-        loss_sum = torch.zeros((), dtype=torch.float64, device=self.device)
-        corr_sum = torch.zeros((), dtype=torch.float64, device=self.device)
+        # per-batch (loss sum, correct count) stay on the device and are reduced once at the end: no host sync and
+        # no extra kernels per batch
+        parts_l, parts_c = [], []
         seen = 0
         for i, (xb, yb) in enumerate(batches):
             if steps is not None and i >= steps:
@@ -416,12 +417,16 @@ class Model:
             xd, yd = st(xb, torch.float32), st(yb)
             st.next_step()
             ls, cs = self._backend.eval_step(xd, yd)
-            loss_sum += ls.to(torch.float64)
-            corr_sum += cs.to(torch.float64)
+            parts_l.append(ls.detach().reshape(()))
+            parts_c.append(cs.detach().reshape(()))
             seen += len(xb)
+        if not parts_l:
+            out = [0.0] + ([0.0] if self._metric_accuracy else [])
+            return out if len(out) > 1 else out[0]
+        loss_sum = torch.stack(parts_l).to(torch.float64).sum()
         out = [float(loss_sum) / max(seen, 1)]
         if self._metric_accuracy:
-            out.append(float(corr_sum) / max(seen, 1))
+            out.append(float(torch.stack(parts_c).to(torch.float64).sum()) / max(seen, 1))
         return out if len(out) > 1 else out[0]
 
     def predict(self, x, batch_size=32, **kwargs):
