@@ -7,8 +7,11 @@ env).  Rank 0 prints ONE JSON line.  The model is the reference's CNN (mnist_ker
 with random-init weights, Adadelta with LR 1.0*size wrapped in DistributedOptimizer
 (mnist_keras.py:84-87); data is synthetic 28x28x1 (no network for MNIST).
 
-Timing: W warm-up steps, then K steps bracketed by barrier + cuda synchronize, timed with
-CUDA events on the launching stream, max over ranks.  Inputs rotate through a device pool
+Timing: W warm-up steps (the last two after the barrier, so that every rank's GPU queue is in lock
+step when the first event is recorded), then K steps bracketed by barrier + cuda synchronize, timed
+with CUDA events on the launching stream, max over ranks.  The clock sampler starts on every rank
+before anything is timed.  `vs_baseline` is value / the stock arm (`--impl torch_nccl`) measured in
+the same run on the same ranks (the reference publishes nothing and cannot be installed).  Inputs rotate through a device pool
 larger than L2 (>= 160 MB) so no step re-reads its batch from cache.  The e2e number
 goes through the public API (``model.train_on_batch_async``, each result awaited one step late) with
 a pinned-host -> device copy of every batch and a device -> host read of the loss every step.
@@ -32,11 +35,14 @@ BATCH = 128
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2000)
-    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=30)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch_nccl"])
     ap.add_argument("--optimizer", default="adadelta", choices=["adadelta", "adam"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-baseline", action="store_true", help="skip the in-run stock arm (vs_baseline stays null)")
+    ap.add_argument("--lr-warmup", action="store_true",
+                    help="drive LearningRateWarmupCallback: the LR changes before every batch (TF2 script config)")
     return ap.parse_args()
 
 
@@ -98,6 +104,25 @@ class ClockSampler:
         self.samples.append((float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)),
                              int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))))
 
+    def mark_begin(self):
+        """Start of a timed region: only samples from here to mark_end() are reported (one is taken now, on
+        the calling thread - before the alignment steps, the same on every rank)."""
+        if self.nvml is not None:
+            try:
+                self._sample()
+            except Exception:
+                pass
+            self._lo = len(self.samples) - 1
+            self._hi = None
+
+    def mark_end(self):
+        if self.nvml is not None:
+            try:
+                self._sample()
+            except Exception:
+                pass
+            self._hi = len(self.samples)
+
     def _poll(self):
         while not self._stop.wait(self.PERIOD):
             try:
@@ -121,9 +146,12 @@ class ClockSampler:
             bits = {"hw_slowdown": n.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": n.nvmlClocksEventReasonHwThermalSlowdown,
                     "sw_thermal_slowdown": n.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": n.nvmlClocksEventReasonSwPowerCap,
                     "hw_power_brake_slowdown": n.nvmlClocksEventReasonHwPowerBrakeSlowdown}
-            sm = sorted(s for s, _ in self.samples[1:]) or sorted(s for s, _ in self.samples)   # [0] predates the region
+            lo = getattr(self, "_lo", None)
+            window = self.samples[lo:getattr(self, "_hi", None)] if lo is not None else self.samples[1:]
+            window = window or self.samples
+            sm = sorted(s for s, _ in window)
             seen = 0
-            for _, r in self.samples[1:]:
+            for _, r in window:
                 seen |= r
             return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz,
                     "reasons": sorted(k for k, b in bits.items() if seen & b), "samples": len(sm), "source": "nvml, 5 ms period"}
@@ -191,6 +219,11 @@ def make_model_ours(hvd, keras, opt_name):
     return m
 
 
+def _bad_clocks(clocks):
+    return bool(clocks) and any(r in ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")
+                                for r in clocks.get("reasons", []))
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -204,14 +237,20 @@ def run_ours(args):
     dev = hvd.device()
     if dev.type != "cuda":
         raise SystemExit("bench.py needs a CUDA device (the CPU oracle is not a benchmark target)")
+    if args.warmup < 3:
+        raise SystemExit("--warmup must be >= 3 (timing rules)")
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cuda.matmul.allow_tf32 = True
+    # The clock sampler (NVML init + polling thread) starts on EVERY rank long before the timed region:
+    # nothing rank-specific may sit between the alignment steps and e0 (round 1 started it on rank 0
+    # only, right before e0, and the other ranks' first fused kernel then waited ~7 ms for rank 0).
+    sampler = ClockSampler(dev.index)
+    sampler.start()
     model = make_model_ours(hvd, keras, args.optimizer)
     rng = np.random.default_rng(1000 + hvd.rank())
     pool_n = 416                                  # 416 * 128 * 784 * 4 B = 167 MB > 126 MB L2
     xs_host = torch.from_numpy(rng.random((pool_n, BATCH, 28, 28, 1), dtype=np.float32)).pin_memory()
     ys_host = torch.from_numpy(rng.integers(0, 10, (pool_n, BATCH)).astype(np.int64)).pin_memory()
-    xs_dev, ys_dev = xs_host.to(dev), ys_host.to(dev)
     model._ensure_built((BATCH, 28, 28, 1))
     hvd.broadcast_global_variables(0, model)
     be = model._backend
@@ -222,52 +261,84 @@ def run_ours(args):
 
     xh_np, yh_np = xs_host.numpy(), ys_host.numpy()
     host_fed = hasattr(be, "train_host_lazy")
+    xs_dev = ys_dev = None
+    if not host_fed:
+        xs_dev, ys_dev = xs_host.to(dev), ys_host.to(dev)
+
+    # --lr-warmup: the TF2 script's configuration (tensorflow2_keras_mnist.py:55,82): the warmup callback
+    # changes the LR before EVERY batch, so the hyper-parameter row is pushed host -> device every step.
+    warm_cb = None
+    if args.lr_warmup:
+        warm_cb = hvd.callbacks.LearningRateWarmupCallback(warmup_epochs=3, verbose=0)
+        warm_cb.set_model(model)
+        total = 2 * (args.warmup + args.steps) + 16
+        warm_cb.set_params({"steps": max(total // 3, 1)})
+        warm_cb.on_train_begin({})
+    step_no = [0]
+
+    def before_step():
+        if warm_cb is not None:
+            spe = warm_cb.steps_per_epoch
+            warm_cb.on_epoch_begin(step_no[0] // spe)
+            warm_cb.on_batch_begin(step_no[0] % spe)
+        step_no[0] += 1
 
     def step(i):
+        before_step()
         if host_fed:
             # the engine's own staging: batch i is copied pinned-host -> device on the copy stream into the
             # input buffers of the next step parity while step i-1 computes; returns device scalars (no sync)
-            return be.train_host_lazy(xh_np[i % pool_n], yh_np[i % pool_n])
-        return be.train_step(xs_dev[i % pool_n], ys_dev[i % pool_n])
+            out = be.train_host_lazy(xh_np[i % pool_n], yh_np[i % pool_n])
+        else:
+            out = be.train_step(xs_dev[i % pool_n], ys_dev[i % pool_n])
+        if warm_cb is not None:
+            warm_cb.on_batch_end(0)
+        return out
 
-    for i in range(args.warmup):
+    align = 2                                       # the last `align` warm-up steps run after the barrier
+    for i in range(args.warmup - align):
         step(i)
-    torch.cuda.synchronize()
-    hvd.barrier()
-    sampler = ClockSampler(dev.index)
-    if hvd.rank() == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    e0.record()
-    for i in range(args.steps):
-        loss, _ = step(args.warmup + i)
-    e1.record()
-    torch.cuda.synchronize()
-    hvd.barrier()
-    ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if hvd.rank() == 0 else None
-    ms_t = torch.tensor([ms], dtype=torch.float64)
-    all_ms = hvd.allgather(ms_t)
-    ms_max = float(all_ms.max())
-    final_loss = float(loss)
 
-    e2e = None
-    if not args.no_e2e:
-        xh = xs_host.numpy()
-        yh = ys_host.numpy()
-        for i in range(max(3, args.warmup // 2)):
-            model.train_on_batch(xh[i % pool_n], yh[i % pool_n])
+    def timed_region(base):
+        """`align` untimed steps that put every rank's GPU queue in lock step (each step's collective
+        is a cross-rank sync), then EXACTLY args.steps timed steps between two events on the launching
+        stream.  Nothing but step launches happens between the barrier and e1."""
         torch.cuda.synchronize()
         hvd.barrier()
+        sampler.mark_begin()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for i in range(align):
+            step(base + i)
+        e0.record()
+        for i in range(args.steps):
+            loss, _ = step(base + align + i)
+        e1.record()
+        torch.cuda.synchronize()
+        sampler.mark_end()
+        hvd.barrier()
+        ms = float(hvd.allgather(torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64)).max())
+        return ms, float(loss)
+
+    ms_max, final_loss = timed_region(args.warmup - align)
+
+    def e2e_region():
         # Public API, pipelined by one step: every step copies ITS batch from pinned host memory to the
         # device and ITS (loss, accuracy, step) lands in pinned host memory (written by a kernel of the
-        # step's backward, 12 bytes); the result of step t is awaited while step t+1 is already enqueued, so the H2D
-        # copy of batch t+1 overlaps the compute of step t.
+        # step's backward, 12 bytes); the result of step t is awaited while step t+1 is already enqueued,
+        # so the H2D copy of batch t+1 overlaps the compute of step t.
+        for i in range(max(3, args.warmup // 2)):
+            before_step()
+            model.train_on_batch(xh_np[i % pool_n], yh_np[i % pool_n])
+        torch.cuda.synchronize()
+        hvd.barrier()
+        for i in range(align):
+            before_step()
+            model.train_on_batch(xh_np[(3 + i) % pool_n], yh_np[(3 + i) % pool_n])
         t0 = time.perf_counter()
         pending = None
         for i in range(args.steps):
-            h = model.train_on_batch_async(xh[(7 + i) % pool_n], yh[(7 + i) % pool_n])
+            before_step()
+            h = model.train_on_batch_async(xh_np[(7 + i) % pool_n], yh_np[(7 + i) % pool_n])
             if pending is not None:
                 out = pending.result()
             pending = h
@@ -275,37 +346,89 @@ def run_ours(args):
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         hvd.barrier()
-        e2e_ms = float(hvd.allgather(torch.tensor([(t1 - t0) * 1e3], dtype=torch.float64)).max())
+        ms = float(hvd.allgather(torch.tensor([(t1 - t0) * 1e3], dtype=torch.float64)).max())
+        return ms, float(out[0])
+
+    e2e = None
+    remeasured = False
+    if not args.no_e2e:
+        e2e_ms, last = e2e_region()
+        # sanity: the device-timed loop cannot be slower than the wall-clocked public-API loop of the same
+        # steps by more than 20% unless something one-off landed in the timed region: take both again once
+        if ms_max / args.steps > 1.2 * e2e_ms / args.steps:
+            remeasured = True
+            ms_max, final_loss = timed_region(args.warmup + args.steps)
+            e2e_ms, last = e2e_region()
+            if ms_max / args.steps > 1.2 * e2e_ms / args.steps:
+                raise SystemExit(f"inconsistent timing: device {ms_max / args.steps:.4f} ms/step vs "
+                                 f"e2e {e2e_ms / args.steps:.4f} ms/step")
         e2e = {"value": BATCH * n * args.steps / (e2e_ms / 1e3), "unit": "images/sec",
                "h2d_bytes_per_step": BATCH * 28 * 28 * 4 + BATCH * 8,
-               "d2h_bytes_per_step": 12, "ms_per_step": e2e_ms / args.steps, "last_loss": float(out[0]),
+               "d2h_bytes_per_step": 12, "ms_per_step": e2e_ms / args.steps, "last_loss": last,
                "api": "Model.train_on_batch_async (result awaited one step late)"}
+    clocks = sampler.stop()
+    if _bad_clocks(clocks):                         # thermal / hw slowdown seen: re-measure once
+        sampler = ClockSampler(dev.index)
+        sampler.start()
+        remeasured = True
+        ms_max, final_loss = timed_region(args.warmup + 2 * args.steps)
+        clocks = sampler.stop()
+
+    # multi-GPU correctness the driver can see: after the timed loops every replica must hold the same bits
+    model._sync_backend()
+    torch.cuda.synchronize()
+    cs = int(model.arena.checksum())
+    all_cs = hvd.allgather_object(cs)
+    identical = all(c == all_cs[0] for c in all_cs)
+    fused = getattr(model.optimizer, "_fused", None)
+    describe = getattr(be, "describe_comm", None) or getattr(fused, "describe", None) or (lambda: ["torch/nccl"])
+    variant_ran = describe()
+
+    # the stock arm on the same ranks, same steps/warmup (BASELINE.json: "the stock NCCL path on the same
+    # workload is the baseline" when the reference does not install) -> vs_baseline
+    baseline = None
+    if not args.no_baseline:
+        try:
+            baseline = stock_loop(args)
+        except Exception as e:                      # the product number must not depend on the baseline arm
+            baseline = {"error": f"{type(e).__name__}: {e}"}
 
     if hvd.rank() == 0:
         val = BATCH * n * args.steps / (ms_max / 1e3)
         gl = (launches_per_step or 0) * args.steps
+        vs = (val / baseline["value"]) if baseline and baseline.get("value") else None
+        if e2e is not None and baseline and baseline.get("e2e"):
+            e2e["vs_baseline"] = e2e["value"] / baseline["e2e"]["value"]
+        lr0 = '1.0' if args.optimizer == 'adadelta' else '0.001'
         line = {"metric": "MNIST-CNN training images/sec", "value": val, "unit": "images/sec",
                 "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "tf32 (fp32 storage, fp32 accumulate/optimizer)",
+                "vs_baseline": vs, "dtype": "tf32 (fp32 storage, fp32 accumulate/optimizer)",
                 "data": "synthetic 28x28x1 (MNIST shape), random-init weights", "impl": "ours",
                 "config": {"model": "mnist_keras.py CNN (conv3x3 32/64, maxpool, dropout, dense 128/10)",
                            "global_batch": BATCH * n, "batch_per_gpu": BATCH, "seq_len": None,
-                           "parallelism": f"dp{n}", "optimizer": f"{args.optimizer} lr={'1.0' if args.optimizer == 'adadelta' else '0.001'}*size",
+                           "parallelism": f"dp{n}",
+                           "optimizer": f"{args.optimizer} lr={lr0}*size" + (" + LearningRateWarmupCallback (LR pushed every step)" if args.lr_warmup else ""),
                            "backend": getattr(be, "name", type(be).__name__),
-                           "allreduce": getattr(getattr(model.optimizer, "_fused", None), "describe", lambda: ["torch/nccl"])(),
+                           "allreduce": variant_ran,
+                           "vs_baseline_is": "value / the stock arm (eager PyTorch cuDNN/cuBLAS TF32 + NCCL all_reduce + torch.optim) "
+                                             "measured in this same run on the same ranks; the reference publishes no numbers and cannot be installed",
                            "l2": ("inputs rotate through a 167 MB pinned host pool (> 126 MB L2), H2D on a copy stream under the previous step"
                                   if host_fed else "inputs rotate through a 167 MB device pool (> 126 MB L2)")},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": gl, "final_loss": final_loss}
+                "clocks": clocks, "e2e": e2e, "gpu_launches": gl, "final_loss": final_loss,
+                "replicas_bit_identical": identical, "variant_ran": variant_ran,
+                "remeasured": remeasured, "baseline": baseline}
         print(json.dumps(line))
     hvd.shutdown()
     return 0
 
 
-def run_torch_nccl(args):
+def stock_loop(args):
     """Stock baseline of record: the same CNN in eager PyTorch
     (cuDNN/cuBLAS, TF32 allowed), gradients averaged with torch.distributed NCCL all_reduce on one
-    flattened bucket, torch.optim Adadelta/Adam.  None of this repo's kernels or engine."""
+    flattened bucket, torch.optim Adadelta/Adam.  None of this repo's kernels or engine.  Uses the
+    default process group when one exists (the `ours` arm calls it on the ranks it just measured),
+    else creates one.  Returns the result dict on every rank."""
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -317,10 +440,12 @@ def run_torch_nccl(args):
     lr_ = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(lr_)
     dev = torch.device("cuda", lr_)
-    if n > 1:
+    own_pg = False
+    if n > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29512")
         dist.init_process_group("nccl", rank=rank, world_size=n, device_id=dev)
+        own_pg = True
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cuda.matmul.allow_tf32 = True
     torch.backends.cudnn.benchmark = True
@@ -367,26 +492,35 @@ def run_torch_nccl(args):
         opt.step()
         return loss
 
+    def barrier():
+        if n > 1:
+            t = torch.zeros(1, device=dev)
+            dist.all_reduce(t)
+        torch.cuda.synchronize()
+
     net.train()
-    for i in range(args.warmup):
-        step(xs_dev[i % pool_n], ys_dev[i % pool_n])
-    torch.cuda.synchronize()
-    if n > 1:
-        dist.barrier()
     sampler = ClockSampler(lr_)
-    if rank == 0:
-        sampler.start()
+    sampler.start()
+    align = 2
+    for i in range(max(args.warmup - align, 1)):
+        step(xs_dev[i % pool_n], ys_dev[i % pool_n])
+    barrier()
+    sampler.mark_begin()
+    for i in range(align):
+        step(xs_dev[i % pool_n], ys_dev[i % pool_n])
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
         loss = step(xs_dev[(args.warmup + i) % pool_n], ys_dev[(args.warmup + i) % pool_n])
     e1.record()
     torch.cuda.synchronize()
+    sampler.mark_end()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if n > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
     # e2e: pinned host batch -> device every step, loss.item() every step
+    barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         x = xs_host[(7 + i) % pool_n].to(dev, non_blocking=True)
@@ -396,21 +530,29 @@ def run_torch_nccl(args):
     e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3], device=dev, dtype=torch.float64)
     if n > 1:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-    if rank == 0:
-        ms_max = float(ms)
-        print(json.dumps({
-            "metric": "MNIST-CNN training images/sec", "value": BATCH * n * args.steps / (ms_max / 1e3),
-            "unit": "images/sec", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "tf32 (cuDNN/cuBLAS allow_tf32)", "data": "synthetic 28x28x1",
-            "impl": "torch_nccl",
-            "config": {"model": "mnist_keras.py CNN, eager PyTorch + NCCL all_reduce + torch.optim",
-                       "global_batch": BATCH * n, "parallelism": f"dp{n}", "optimizer": args.optimizer},
-            "clocks": clocks, "gpu_launches": 0,
-            "e2e": {"value": BATCH * n * args.steps / (float(e2e_ms) / 1e3), "unit": "images/sec",
-                    "h2d_bytes_per_step": BATCH * 784 * 4 + BATCH * 8, "d2h_bytes_per_step": 4}}))
-    if n > 1:
+    ms_max = float(ms)
+    out = {
+        "metric": "MNIST-CNN training images/sec", "value": BATCH * n * args.steps / (ms_max / 1e3),
+        "unit": "images/sec", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "tf32 (cuDNN/cuBLAS allow_tf32)", "data": "synthetic 28x28x1",
+        "impl": "torch_nccl",
+        "config": {"model": "mnist_keras.py CNN, eager PyTorch + NCCL all_reduce + torch.optim",
+                   "global_batch": BATCH * n, "parallelism": f"dp{n}", "optimizer": args.optimizer},
+        "clocks": clocks, "gpu_launches": 0,
+        "e2e": {"value": BATCH * n * args.steps / (float(e2e_ms) / 1e3), "unit": "images/sec",
+                "ms_per_step": float(e2e_ms) / args.steps,
+                "h2d_bytes_per_step": BATCH * 784 * 4 + BATCH * 8, "d2h_bytes_per_step": 4}}
+    del net, opt, xs_dev, ys_dev
+    if own_pg:
         dist.destroy_process_group()
+    return out
+
+
+def run_torch_nccl(args):
+    out = stock_loop(args)
+    if int(os.environ.get("RANK", 0)) == 0:
+        print(json.dumps(out))
     return 0
 
 

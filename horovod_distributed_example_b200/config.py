@@ -70,8 +70,12 @@ class Config:
     nvtx: bool = False                 # NVTX ranges around steps / buckets / collectives
     #: "rank:step" - that rank skips its collective at that step (tests the watchdog).
     fault_inject: Optional[str] = None
-    #: seconds an in-kernel barrier may spin before it gives up and flags an error.
+    #: seconds after which a rank that is still waiting for its peers logs a WARNING (Horovod's
+    #: HOROVOD_STALL_CHECK_TIME_SECONDS: a warning, not an abort).
     stall_check_time: float = 60.0
+    #: seconds after which an in-kernel barrier gives up, raises the error word and aborts the collective
+    #: (HOROVOD_STALL_SHUTDOWN_TIME_SECONDS).  0 = ten times the warning time (600 s by default), so a
+    #: rank-0-only pause such as a large checkpoint or an export cannot corrupt the other ranks.
     stall_shutdown_time: float = 0.0
     #: symmetric-memory backend: auto | vmm | ipc
     symm_backend: str = "auto"
@@ -104,6 +108,12 @@ class Config:
         c.autotune = _env_bool("AUTOTUNE")
         c.comm_ctas = _env_int("COMM_CTAS", 0)
         return c
+
+    def barrier_abort_time(self) -> float:
+        """Seconds an in-kernel barrier may spin before it aborts (0 = spin forever)."""
+        if self.stall_shutdown_time > 0:
+            return self.stall_shutdown_time
+        return 10.0 * self.stall_check_time if self.stall_check_time > 0 else 0.0
 
     def parsed_fault(self):
         """Return (rank, step) from HVD_FAULT_INJECT or None."""

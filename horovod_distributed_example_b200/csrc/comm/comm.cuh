@@ -4,8 +4,10 @@
 // signal pad.  Kernels synchronise with monotonically increasing epoch counters written
 // with st.release.sys into the peers' pads and polled with ld.acquire.sys on the local pad
 // (no 0/1 flags -> no ABA under CUDA-graph replay).  Spins are
-// bounded: on timeout the kernel raises an error word in host-visible memory and moves
-// on instead of hanging the GPU (stall inspector equivalent).
+// bounded: on timeout the kernel raises an error word in host-visible memory and ABORTS - it
+// returns without reducing, updating, storing to peers or advancing its epoch, so parameters and
+// optimizer state stay as they were when the host reads the error word (stall inspector
+// equivalent).  The bound is the shutdown time, not the 60 s warning time.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -75,12 +77,15 @@ __device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
 // for all of them: no grid-wide sync, and the only co-residency requirement is that CTA b
 // of each rank eventually runs (grid <= resident capacity, enforced by the launcher).
 //   release=true : make this CTA's earlier global/peer stores visible first.
-__device__ __forceinline__ void hvd_barrier(const HvdCommCtx& c, int slot, uint32_t epoch, bool release) {
+// Returns false (for the whole CTA) when a peer did not arrive within timeout_ns, or when another CTA /
+// an earlier kernel already raised the error word: the caller must return without touching anything.
+__device__ __forceinline__ bool hvd_barrier(const HvdCommCtx& c, int slot, uint32_t epoch, bool release) {
   const int rank = hvd_rank(c);
   const int cta = blockIdx.x;
-  if (c.nranks == 1) { __syncthreads(); return; }        // single GPU: nothing to wait for
+  if (c.nranks == 1) { __syncthreads(); return true; }   // single GPU: nothing to wait for
   if (release) __threadfence_system();
   __syncthreads();
+  int failed = 0;
   if ((int)threadIdx.x < c.nranks) {
     const int peer = threadIdx.x;
     st_release_sys(hvd_flag(c, peer, slot, cta, rank), epoch);
@@ -94,12 +99,14 @@ __device__ __forceinline__ void hvd_barrier(const HvdCommCtx& c, int slot, uint3
         else if (now - t0 > c.timeout_ns) {
           // error word: 1-based missing peer in the low byte, slot above it
           atomicCAS((int*)c.error, 0, (slot << 8) | (peer + 1));
+          failed = 1;
           break;
         }
+        if (*(volatile int*)c.error != 0) { failed = 1; break; }     // somebody else already gave up
       }
     }
   }
-  __syncthreads();
+  return __syncthreads_or(failed) == 0;
 }
 
 __device__ __forceinline__ uint32_t hvd_epoch_load(const HvdCommCtx& c, int slot) {

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256, 2) hvd_fused_kernel(HvdCommCtx c, HvdFuse
   const int N = c.nranks;
   const uint32_t ep = hvd_epoch_load(c, a.slot);
   // entry barrier: every rank's backward has finished writing this bucket
-  hvd_barrier(c, a.slot, ep + 1, false);
+  if (!hvd_barrier(c, a.slot, ep + 1, false)) return;     // timed out: abort with params/state/epoch untouched
 
   long long s = a.start, e = a.end;
   if (VARIANT != HVD_ONESHOT) {
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(256, 2) hvd_fused_kernel(HvdCommCtx c, HvdFuse
   if (VARIANT != HVD_ONESHOT || a.exit_barrier) {
     // exit barrier: (two-shot/NVLS) every owner's stores have landed in every arena;
     // (one-shot) every rank has finished reading my gradients.
-    hvd_barrier(c, a.slot, ep + 2, VARIANT != HVD_ONESHOT);
+    if (!hvd_barrier(c, a.slot, ep + 2, VARIANT != HVD_ONESHOT)) return;
     next = ep + 2;
   }
   hvd_epoch_store(c, a.slot, next);
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(256, 2) hvd_fused_kernel(HvdCommCtx c, HvdFuse
 __global__ void __launch_bounds__(512) hvd_bcast_kernel(HvdCommCtx c, int slot, int root, long long off, long long n) {
   const int rank = hvd_rank(c);
   const uint32_t ep = hvd_epoch_load(c, slot);
-  hvd_barrier(c, slot, ep + 1, false);
+  if (!hvd_barrier(c, slot, ep + 1, false)) return;
   if (rank != root) {
     const long long n4 = n / 4;
     const float* src = c.base[root] + off;
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(512) hvd_bcast_kernel(HvdCommCtx c, int slot, 
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x)
       *reinterpret_cast<float4*>(dst + i * 4) = ld_sys_f4(src + i * 4);
   }
-  hvd_barrier(c, slot, ep + 2, false);     // root may modify its data again
+  if (!hvd_barrier(c, slot, ep + 2, false)) return;     // root may modify its data again
   hvd_epoch_store(c, slot, ep + 2);
 }
 

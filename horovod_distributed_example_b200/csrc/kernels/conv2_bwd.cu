@@ -597,10 +597,10 @@ extern "C" int hvd_conv2_dgrad(const float* dy2, const float* w2, const float* a
     uint32_t wb[2] = {32, 32};
     if (tc::make_tmap(&tmW, w2, 2, wd, ws, wb)) return -3;
   }
-  static bool attr = false;
-  if (!attr) {
+  static tc::PerDeviceOnce attr;
+  if (attr.need()) {
     if (cudaFuncSetAttribute(dg::conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dg::SMEM_BYTES) != cudaSuccess) return -10;
-    attr = true;
+    attr.mark();
   }
   dg::Params p{B, B * dg::TILES_PER_IMG, a1, da1, x, g_w1, g_b1, -1, 0};
   if (ctas <= 0) ctas = 148;
@@ -628,10 +628,10 @@ extern "C" int hvd_conv2_wgrad_ex(const float* a1, const float* dy2, float* g_w,
     uint32_t box[5] = {32, 8, 2, 28, 1};
     if (tc::make_tmap(&tmG, dy2, 5, gd, gs, box, true)) return -3;
   }
-  static bool attr = false;
-  if (!attr) {
+  static tc::PerDeviceOnce attr;
+  if (attr.need()) {
     if (cudaFuncSetAttribute(wg::conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wg::SMEM_BYTES) != cudaSuccess) return -10;
-    attr = true;
+    attr.mark();
   }
   wg::Params p;
   p.B = B; p.n_strips = B * 3; p.n_w = 0;
@@ -667,10 +667,10 @@ extern "C" int hvd_conv2_bwd(const float* dy2, const float* w2, const float* a1,
     uint32_t wb[2] = {32, 32};
     if (tc::make_tmap(&tmW_d, w2, 2, wd, ws, wb)) return -5;
   }
-  static bool attr = false;
-  if (!attr) {
+  static tc::PerDeviceOnce attr;
+  if (attr.need()) {
     if (cudaFuncSetAttribute(conv2_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_SMEM) != cudaSuccess) return -10;
-    attr = true;
+    attr.mark();
   }
   if (ctas <= 0) ctas = 148;
   const int n_tiles = B * dg::TILES_PER_IMG;

@@ -217,10 +217,10 @@ extern "C" int hvd_conv2_fprop(const float* a1, const float* w2, const float* bi
     uint32_t wb[2] = {32, 32};
     if (tc::make_tmap(&tmW, w2, 2, wd, ws, wb, true)) return -3;
   }
-  static bool attr = false;
-  if (!attr) {
+  static tc::PerDeviceOnce attr;
+  if (attr.need()) {
     if (cudaFuncSetAttribute(conv2_fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess) return -10;
-    attr = true;
+    attr.mark();
   }
   Params p;
   p.B = B; p.n_tiles = ((B + 1) / 2) * 9; p.training = training; p.keep = keep; p.bias = bias2; p.p2 = p2; p.mask = mask;

@@ -62,6 +62,8 @@ extern "C" int hvd_dense_forward(const float* x, const float* W, const float* bi
 //     HVD_ERR_NOALLOC_TOO_LARGE and a message from hvd_dense_forward_noalloc_error().
 //   * The first call on each device looks up the array's device address (one-time set-up, with that
 //     device current).  Make that first call before you begin any stream capture on the device.
+//   * The array used is the one of the device that is CURRENT when you call; `stream` must belong to
+//     that device (checked: a stream of another device is refused with HVD_ERR_NOALLOC_SETUP).
 //   * All calls on a device share the one array and it keeps whatever the previous call left in it;
 //     this function therefore clears the part it is about to use, on `stream`, before the GEMM.
 //     Two calls whose GPU work can overlap (different streams, or different host threads without
@@ -125,15 +127,34 @@ extern "C" int hvd_dense_forward_noalloc(const float* x, const float* W, const f
                     " floats; use hvd_dense_forward with your own scratch buffer";
     return HVD_ERR_NOALLOC_TOO_LARGE;
   }
+  if ((N & 3) || (K & 3)) {                // checked here so that nothing is enqueued for a call that is refused
+    g_noalloc_err = "hvd_dense_forward_noalloc: N and K must be multiples of 4 (16-byte row strides for TMA)";
+    return -2;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  // The array that is used is the CURRENT device's.  A stream that belongs to another device would make the
+  // kernels run there with this device's address: refuse instead of touching the wrong GPU's memory.
+  {
+    int cur = -1, sdev = -1;
+    if (cudaGetDevice(&cur) == cudaSuccess && cudaStreamGetDevice(st, &sdev) == cudaSuccess && sdev != cur) {
+      g_noalloc_err = "hvd_dense_forward_noalloc: the stream belongs to device " + std::to_string(sdev) +
+                      " but device " + std::to_string(cur) + " is current; make the stream's device current first";
+      return HVD_ERR_NOALLOC_SETUP;
+    }
+    cudaGetLastError();                    // a failed query is not an error of this call
+  }
   float* scratch = nullptr;
   int rc = noalloc_scratch_for_current_device(&scratch);
   if (rc != 0) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
   // shared array, previous contents unknown: the accumulator region must start at zero
   cudaError_t e = cudaMemsetAsync(scratch, 0, (size_t)need * sizeof(float), st);
   if (e != cudaSuccess) {
     g_noalloc_err = std::string("clearing the scratch failed: ") + cudaGetErrorString(e);
     return (int)e;
   }
-  return hvd_dense_forward_impl(x, W, bias, y, M, N, K, relu, k_split, scratch, st);
+  rc = hvd_dense_forward_impl(x, W, bias, y, M, N, K, relu, k_split, scratch, st);
+  if (rc != 0)
+    g_noalloc_err = "hvd_dense_forward_noalloc: the GEMM or its finalize pass failed with code " + std::to_string(rc) +
+                    (rc > 0 ? std::string(" (") + cudaGetErrorString((cudaError_t)rc) + ")" : std::string(" (tensor-map or argument error)"));
+  return rc;
 }

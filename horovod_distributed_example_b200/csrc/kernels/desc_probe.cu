@@ -78,10 +78,10 @@ extern "C" int hvd_desc_probe(const float* Ag, const float* Bg, float* D, int a_
   uint32_t bb[2] = {32, 64};
   if (tc::make_tmap(&tb, Bg, 2, bd, str, bb, false)) return -3;
   const int smem = 65536 + 8192 + 1024 + 128;
-  static bool attr = false;
-  if (!attr) {
+  static tc::PerDeviceOnce attr;
+  if (attr.need()) {
     if (cudaFuncSetAttribute(desc_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -10;
-    attr = true;
+    attr.mark();
   }
   ProbeParams p{a_mn, rows_a, shift_rows, lbo, sbo, base_offset, D};
   desc_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(ta, tb, p);

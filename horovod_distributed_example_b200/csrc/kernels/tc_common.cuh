@@ -177,6 +177,18 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, int a_mn_ma
 #include <string.h>
 #include <utility>
 namespace tc {
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device (per-context) setting: a launcher that
+// remembers "done" per process would skip it on a second GPU of the same process (C/C++ callers of the
+// C ABI, emulated multi-device tests) and every launch there would fail.  Remembered per device ordinal.
+struct PerDeviceOnce {
+  bool done[64] = {};
+  int dev = -1;
+  bool need() {
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { dev = -1; return true; }
+    return !done[dev];
+  }
+  void mark() { if (dev >= 0) done[dev] = true; }
+};
 inline bool pdl_enabled() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("HVD_PDL"); v = (e && e[0] == '0') ? 0 : 1; }

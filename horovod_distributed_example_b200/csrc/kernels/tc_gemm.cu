@@ -217,10 +217,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 template <int BN, bool A_MN, bool B_MN>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
   auto k = tc_gemm_kernel<BN, A_MN, B_MN>;
-  static bool attr = false;
-  if (!attr) {
+  static tc::PerDeviceOnce attr;
+  if (attr.need()) {
     if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<BN>::TOTAL) != cudaSuccess) return -10;
-    attr = true;
+    attr.mark();
   }
   dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN, p.k_split);
   return (int)tc::launch_pdl(k, grid, dim3(384), Smem<BN>::TOTAL, st, ta, tb, p);

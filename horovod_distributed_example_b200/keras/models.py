@@ -188,6 +188,11 @@ class Model:
             eng = mnist_cnn.maybe_engine(self)
             if eng is not None:
                 return eng
+            # Not silent: everything below runs on stock torch ops (cuDNN/cuBLAS); only the optimizer path
+            # (arena + fused allreduce/update buckets) is this framework's own code for such models.
+            from .. import basics
+            basics.log.warning("model %s does not match the fused sm_100a MNIST engine (%s); its forward/backward "
+                               "run on torch autograd (cuDNN/cuBLAS)", self.name, mnist_cnn.why_not(self))
         return _TorchBackend(self)
 
     def _ensure_built(self, x_shape):
@@ -632,7 +637,10 @@ class _TorchBackend:
         if getattr(opt, "_hooked", False):
             # a fused bucket kernel of the previous step may still be reading the gradient slab on the side stream
             torch.cuda.current_stream(m.device).wait_stream(opt._fused.side_stream)
-        arena.grads.zero_()
+        # backward_passes_per_step > 1: gradients keep accumulating in the slab over the passes of a cycle
+        # (the wrapper only reduces + applies on the last one), so the slab is cleared on the first pass only
+        if getattr(opt, "_pass", 0) % getattr(opt, "_bpps", 1) == 0:
+            arena.grads.zero_()
         if hasattr(opt, "begin_step"):
             opt.begin_step()
         with torch.enable_grad():

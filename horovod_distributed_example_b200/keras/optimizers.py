@@ -90,8 +90,11 @@ class Optimizer:
         # kernel of step t (possibly still running on a side stream) never sees step t+1's values
         self._hyper = torch.zeros(2, 8, dtype=torch.float32, device=arena.device)
         self._next_slot = 0
-        self._pin_ring = [torch.zeros(8, dtype=torch.float32).pin_memory() for _ in range(8)] \
+        # ring of pinned staging rows for the async H2D pushes; each entry carries the event of its last
+        # copy, waited for before the entry is rewritten (the host may run many steps ahead of the device)
+        self._pin_ring = [torch.zeros(8, dtype=torch.float32).pin_memory() for _ in range(16)] \
             if arena.device.type == "cuda" else None
+        self._pin_ev = [None] * 16
         self._pin_i = 0
         self._push_hyper(both=True)
 
@@ -118,11 +121,18 @@ class Optimizer:
         rows = (0, 1) if both else (self._next_slot,)
         if self._hyper.is_cuda:
             # tiny async H2D from a ring of pinned buffers; ordered on the current stream
-            buf = self._pin_ring[self._pin_i % len(self._pin_ring)]
+            k = self._pin_i % len(self._pin_ring)
+            buf = self._pin_ring[k]
             self._pin_i += 1
+            ev = self._pin_ev[k]
+            if ev is not None:
+                ev.synchronize()          # the copy that last read this entry has executed (normally long ago)
             buf.copy_(vals)
             for r in rows:
                 self._hyper[r].copy_(buf, non_blocking=True)
+            if ev is None:
+                ev = self._pin_ev[k] = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self._hyper.device))
         else:
             for r in rows:
                 self._hyper[r].copy_(vals)

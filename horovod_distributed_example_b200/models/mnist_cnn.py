@@ -85,17 +85,28 @@ def matches(model) -> bool:
     return bool(ok)
 
 
-def maybe_engine(model):
-    """Return a ``MnistEngine`` for ``model`` or None (generic torch-autograd path)."""
+def why_not(model) -> str:
+    """Why ``model`` does not run on the fused engine ('' when it does)."""
     if os.environ.get("HVD_ENGINE", "native") != "native":
-        return None
-    if model.device.type != "cuda" or not matches(model):
-        return None
+        return "HVD_ENGINE is not 'native'"
+    if model.device.type != "cuda":
+        return "not on a CUDA device"
+    if not matches(model):
+        return "layer stack differs from the reference CNN (Conv32-Conv64-MaxPool-Dropout-Flatten-Dense128-Dropout-Dense10 on 28x28x1)"
     name = losses_mod.loss_name(model.loss) if model.loss is not None else ""
     if "categorical_crossentropy" not in name or getattr(model.loss, "from_logits", False):
-        return None
+        return "loss is not (sparse_)categorical_crossentropy on probabilities"
+    if getattr(model.optimizer, "_bpps", 1) != 1:
+        return "backward_passes_per_step > 1"
     if torch.cuda.get_device_capability(model.device)[0] < 10:
-        return None                      # tcgen05/TMEM kernels need sm_100a
+        return "device is older than sm_100 (tcgen05/TMEM kernels)"
+    return ""
+
+
+def maybe_engine(model):
+    """Return a ``MnistEngine`` for ``model`` or None (generic torch-autograd path)."""
+    if why_not(model):
+        return None
     return MnistEngine(model)
 
 
@@ -120,10 +131,19 @@ class _StepResult:
             if e._train_steps - seq >= 16:
                 raise RuntimeError("step result was overwritten: resolve handles within 16 steps")
             t0 = time.monotonic()
+            warned = False
+            spins = 0
             while int(slot_u[2]) != seq:
-                if time.monotonic() - t0 > e._result_timeout:
-                    if e.fused is not None:
-                        e.fused.ctx.check_error()          # a stalled peer is the usual reason: name it
+                spins += 1
+                if spins & 0xfff:
+                    continue
+                waited = time.monotonic() - t0
+                if e.fused is not None:
+                    e.fused.ctx.check_error()              # an in-kernel barrier gave up: names the stalled peer
+                if not warned and waited > e._stall_warn:
+                    warned = True                          # Horovod's stall inspector: a warning, not an abort
+                    basics.log.warning("step %d has been waiting for %.0f s (stalled or slow peer?)", seq, waited)
+                if waited > e._result_timeout:
                     raise RuntimeError(f"step {seq} did not finish within {e._result_timeout:.0f} s")
         self._val = (float(slot_f[0]), float(slot_f[1]))
         return self._val
@@ -223,7 +243,9 @@ class MnistEngine:
         cfg = basics.state().config
         self._fault = cfg.parsed_fault() if cfg is not None else None
         self._debug = cfg is not None and bool(cfg.debug_checksum or cfg.debug_poison)
-        self._result_timeout = float(cfg.stall_check_time) if cfg is not None and cfg.stall_check_time > 0 else 60.0
+        self._stall_warn = float(cfg.stall_check_time) if cfg is not None and cfg.stall_check_time > 0 else 60.0
+        abort = cfg.barrier_abort_time() if cfg is not None else 0.0
+        self._result_timeout = (abort + 5.0) if abort > 0 else 3600.0     # the in-kernel abort fires first
         self.use_graph = os.environ.get("HVD_NO_GRAPH", "0") != "1" and self.fused is not None
         if self.fused is not None:
             opt._defer_push = True           # hyper-parameter rows are written at step start (see _run_step)

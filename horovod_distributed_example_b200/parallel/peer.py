@@ -457,6 +457,24 @@ class PeerContext:
 
     def allreduce_(self, t: torch.Tensor, average: bool = True) -> torch.Tensor:
         """In-place allreduce of an arbitrary CUDA tensor through the staging buffer."""
+        if t.dtype == torch.float64:
+            # The kernels sum fp32.  A float64 tensor (the metric vector) travels as three fp32 pieces of
+            # <= 18 significant bits each, so the fp32 sum of up to 8 ranks' pieces is exact whenever the
+            # ranks' values are within a factor of 8 of each other (metrics are); recombined in fp64.
+            pieces, rest = [], t.reshape(-1).clone()
+            for _ in range(2):
+                hi = (rest.to(torch.float32).view(torch.int32) & ~0x3F).view(torch.float32)
+                pieces.append(hi)
+                rest = rest - hi.to(torch.float64)
+            pieces.append(rest.to(torch.float32))
+            packed = torch.cat(pieces)
+            self.allreduce_(packed, average=False)
+            n = t.numel()
+            tot = packed[:n].to(torch.float64) + packed[n:2 * n].to(torch.float64) + packed[2 * n:].to(torch.float64)
+            if average:
+                tot = tot / self.size
+            t.copy_(tot.view(t.shape))
+            return t
         buf, off = self.buffer_of(t)
         flat = t.reshape(-1) if t.is_contiguous() else None
         if buf is not None and flat is not None and t.dtype == torch.float32 and off % 4 == 0 \
@@ -560,7 +578,7 @@ def context() -> PeerContext:
         st = basics.state()
         try:
             _ctx = PeerContext(st.rank, st.size, st.device, backend=st.config.symm_backend,
-                               timeout_s=st.config.stall_check_time)
+                               timeout_s=st.config.barrier_abort_time())
         except Exception as e:
             _unavailable_reason = str(e)
             raise

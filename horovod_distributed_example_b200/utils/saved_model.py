@@ -36,17 +36,6 @@ def export(model, export_path: str, inputs=None, outputs=None, tags=(SERVING,), 
     with open(os.path.join(export_path, "signature.json"), "w") as f:
         json.dump(sig, f, indent=1)
     if torchscript:
-        class _Infer(torch.nn.Module):
-            def __init__(self, m):
-                super().__init__()
-                self.m = m
-                self.weights = torch.nn.ParameterList(
-                    [torch.nn.Parameter(m.arena.param(n).detach().clone().cpu(), requires_grad=False)
-                     for n in m.trainable_weight_names()])
-
-            def forward(self, x):
-                return self.m._forward(x, False)
-
         cpu_model = _cpu_copy(model)
         example = torch.zeros((1,) + tuple(model.input_shape))
         with torch.no_grad():

@@ -176,8 +176,10 @@ int hvd_dense_forward(const float* x, const float* W, const float* bias, float* 
  * hvd_dense_forward minus `scratch`: the accumulator is a 1 MiB array built into libhvd_cuda.so (held
  * by every GPU that loads the library until exit).  Limit: M*N <= hvd_dense_forward_noalloc_max_elems()
  * (262144); larger sizes return -100 with a message in hvd_dense_forward_noalloc_error().  The first
- * call on a device does a one-time address look-up - make it before any stream capture.  All calls on
- * a device share the array: calls whose GPU work may overlap race. */
+ * call on a device does a one-time address look-up - make it before any stream capture.  The array
+ * used is that of the device that is current at the call, and `stream` must belong to that device (a
+ * stream of another device is refused with -101).  All calls on a device share the array: calls whose
+ * GPU work may overlap race.  Every refusal or failure leaves a message in ..._noalloc_error(). */
 int hvd_dense_forward_noalloc(const float* x, const float* W, const float* bias, float* y, int M, int N, int K,
                               int relu, int k_split, void* stream);
 long long hvd_dense_forward_noalloc_max_elems(void);

@@ -80,3 +80,29 @@ def test_size1_skips_allreduce(hvd_single):
     a.grad("w").fill_(1.0)
     d.apply_gradients(a)
     assert torch.allclose(a.param("w"), before - 0.5)
+
+
+def test_backward_passes_per_step_accumulates(hvd_single):
+    """DistributedOptimizer(backward_passes_per_step=2): two batches accumulate into ONE update that equals
+    a single step on the sum of their gradients (round-1 bug: the slab was cleared on every pass)."""
+    from horovod_distributed_example_b200 import keras
+
+    def run(bpps, batches):
+        keras.backend.clear_session()
+        m = keras.Sequential([keras.layers.Dense(2, use_bias=False, input_shape=(2,))], seed=3)
+        opt = hvd_single.DistributedOptimizer(O.SGD(lr=1.0), backward_passes_per_step=bpps)
+        m.compile(loss=keras.losses.mean_squared_error, optimizer=opt)
+        m.build()
+        m.set_weights([np.zeros((2, 2), np.float32)])
+        for x, y in batches:
+            m.train_on_batch(x, y)
+        return m.get_weights()[0]
+
+    x1, y1 = np.array([[1., 0.]], np.float32), np.array([[1., 1.]], np.float32)
+    x2, y2 = np.array([[0., 1.]], np.float32), np.array([[1., 1.]], np.float32)
+    w_acc = run(2, [(x1, y1), (x2, y2)])
+    # oracle: weights stay at zero during both passes, so the accumulated gradient is g(x1) + g(x2) at w = 0
+    w1 = run(1, [(x1, y1)])
+    w2 = run(1, [(x2, y2)])
+    np.testing.assert_allclose(w_acc, w1 + w2, rtol=1e-6, atol=1e-7)
+    assert np.abs(w_acc[0]).sum() > 0 and np.abs(w_acc[1]).sum() > 0      # neither pass was dropped
