@@ -40,6 +40,11 @@ class BroadcastGlobalVariablesCallback(Callback):
             m = self.model
             m._sync_backend()
             arena = m.arena
+            opt = m.optimizer
+            if basics.rank() == self.root_rank and opt is not None and hasattr(opt, "materialize_state"):
+                # optimizer state of owner-updated ranges lives with its owners: the root completes its copy
+                # (one-sided peer reads) before it becomes everybody's state
+                opt.materialize_state()
             with torch.no_grad():
                 collectives.broadcast_(arena.params, self.root_rank, name="broadcast.params")
                 for i, s in enumerate(arena.slots):

@@ -14,6 +14,15 @@
 //   warp 2 : TMEM allocator
 //   warps 4-11: epilogue           (tcgen05.ld 32x32b -> registers -> fused epilogue -> global; two warps
 //                                   per TMEM lane quadrant, each taking every other 32-column chunk)
+//
+// Two hooks tie it into the pipelined data-parallel step (comm/pipeline.cuh):
+//   EPI_RS_PUSH : the epilogue stages the 128 x 128 tile in shared memory and writes it, as whole 512-byte
+//                 rows, into the receive area of the rank that owns those weight rows - local memory or a peer
+//                 GPU over NVLink - then raises a per-tile flag there (GEMM -> reduce-scatter in one kernel);
+//   wait        : the TMA producer first waits until the weights it is about to read have been delivered by
+//                 their owners (a counter the previous step's tail kernels bump), instead of those kernels
+//                 sitting in an exit barrier.
+#include "comm/pipeline.cuh"
 #include "tc_common.cuh"
 
 namespace {
@@ -26,7 +35,7 @@ constexpr int STAGES = 4;
 // dropped-out activations, row = sample, column = flat (ph,pw,c)) is routed through the mask byte
 // written by conv2_fprop: scaled by 1/keep where live, placed at the arg-max of its 2x2 window,
 // zeros at the other three positions - MaxPool/Dropout/ReLU backward fused into the dgrad epilogue.
-enum Epilogue { EPI_STORE = 0, EPI_ATOMIC_ADD = 1, EPI_BIAS_RELU = 2, EPI_UNPOOL = 3 };
+enum Epilogue { EPI_STORE = 0, EPI_ATOMIC_ADD = 1, EPI_BIAS_RELU = 2, EPI_UNPOOL = 3, EPI_RS_PUSH = 4 };
 
 struct GemmParams {
   int M, N, K;
@@ -38,6 +47,8 @@ struct GemmParams {
   uint32_t lbo_a, sbo_a, lbo_b, sbo_b;   // 0 = default (test hook for descriptor bring-up)
   const uint8_t* mask;                   // EPI_UNPOOL
   float scale;                           // EPI_UNPOOL: 1/keep
+  HvdRsPush rs;                          // EPI_RS_PUSH
+  HvdParamWait wait;                     // counter == nullptr: no wait
 };
 
 template <int BN>
@@ -88,6 +99,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (warp == 0) {
     if (tc::elect_one()) {
+      hvd_param_wait(p.wait);
       for (int i = 0; i < nkb; i++) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
@@ -185,6 +197,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         __syncwarp();                                          // the next column chunk reuses T / Mw
+      } else if (p.epilogue == EPI_RS_PUSH) {
+        // stage the tile row-major in the (now idle) operand ring, 16-byte chunks XOR-swizzled by the row so
+        // that neither these per-row writes nor the per-row reads below conflict on banks
+        float4* T = reinterpret_cast<float4*>(smem);
+        const int rl = q * 32 + lane;
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+          T[rl * 32 + (((c >> 2) + j) ^ lane)] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
       } else if (row < p.M) {
         float* d = p.D + (long long)row * p.ldd + n0 + c;
         if (p.epilogue == EPI_ATOMIC_ADD) {
@@ -209,6 +229,31 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   }
+  if (warp >= 4 && p.epilogue == EPI_RS_PUSH) {
+    // all 8 epilogue warps: tile staged -> every warp store is one whole 512-byte row of the destination
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const HvdRsPush& rs = p.rs;
+    const int tile = blockIdx.x;
+    const int owner = tile / rs.tiles_per_owner, tl = tile - owner * rs.tiles_per_owner;
+    float* dst = rs.recv[owner] + (long long)rs.rank * rs.shard_elems + (long long)tl * (BM * 128);
+    const float4* T = reinterpret_cast<const float4*>(smem);
+    const int w = warp - 4;
+#pragma unroll 4
+    for (int r = w * 16; r < w * 16 + 16; r++)
+      reinterpret_cast<float4*>(dst + r * 128)[lane] = T[r * 32 + (lane ^ (r & 31))];
+    if (rs.nranks > 1 && rs.send_flags) {
+      // every epilogue thread's rows happen-before the barrier; the release below is cumulative over them, so
+      // one system fence (inside st.release.sys) is enough - no fence per thread
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 128) {                    // the owner is told that the tile has landed
+        uint32_t* ep = rs.epoch + HVD_SLOT_RS_PUSH * HVD_MAX_CTAS + tile;
+        const uint32_t e = *ep + 1;
+        if (owner != rs.rank)
+          st_release_sys(rs.pad[owner] + ((size_t)(HVD_SLOT_RS_PUSH * HVD_MAX_CTAS + tl) * HVD_MAX_RANKS + rs.rank), e);
+        *ep = e;
+      }
+    }
+  }
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 2) tc::tmem_dealloc<BN>(tmem);
@@ -230,11 +275,17 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cu
 
 // A: [M][K] (a_mn=0) or [K][M] (a_mn=1); B: [N][K] (b_mn=0) or [K][N] (b_mn=1); all dense row-major fp32.
 // M/N/K tails are zero-filled by TMA (out-of-bounds box elements) and masked in the epilogue.
-extern "C" int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int bn,
-                           int k_split, int epilogue, const float* bias, long long ldd, void* stream,
-                           unsigned lbo_a, unsigned sbo_a, unsigned lbo_b, unsigned sbo_b, const uint8_t* mask,
-                           float scale) {
+extern "C" int hvd_tc_gemm_ex(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int bn,
+                              int k_split, int epilogue, const float* bias, long long ldd, void* stream,
+                              unsigned lbo_a, unsigned sbo_a, unsigned lbo_b, unsigned sbo_b, const uint8_t* mask,
+                              float scale, const HvdRsPush* rs, const HvdParamWait* wait) {
   if ((bn != 64 && bn != 128) || k_split < 1 || K < 1) return -1;
+  if (epilogue == EPI_RS_PUSH) {
+    // whole 128 x 128 tiles of a [M][128] result, one owner per run of tiles
+    if (!rs || bn != 128 || N != 128 || (M % BM) != 0 || k_split != 1 || rs->nranks < 1 || rs->nranks > HVD_MAX_RANKS ||
+        rs->tiles_per_owner < 1 || (M / BM) != rs->tiles_per_owner * rs->nranks || (M / BM) > HVD_MAX_CTAS)
+      return -5;
+  }
   CUtensorMap ta, tb;
   {
     uint64_t dims[2], str[1];
@@ -246,11 +297,21 @@ extern "C" int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int 
     else { dims[0] = N; dims[1] = K; str[0] = (uint64_t)N * 4; box[0] = 32; box[1] = BK; }
     if (tc::make_tmap(&tb, B, 2, dims, str, box, b_mn != 0)) return -3;
   }
-  GemmParams p{M, N, K, k_split, D, ldd ? ldd : (long long)N, bias, epilogue, lbo_a, sbo_a, lbo_b, sbo_b, mask, scale};
+  GemmParams p{M, N, K, k_split, D, ldd ? ldd : (long long)N, bias, epilogue, lbo_a, sbo_a, lbo_b, sbo_b, mask, scale, {}, {}};
+  if (rs) p.rs = *rs;
+  if (wait) p.wait = *wait;
   cudaStream_t st = (cudaStream_t)stream;
 #define HVD_CASE(BN_, AM, BMN) if (bn == BN_ && a_mn == AM && b_mn == BMN) return launch<BN_, AM != 0, BMN != 0>(ta, tb, p, st);
   HVD_CASE(64, 0, 0) HVD_CASE(64, 0, 1) HVD_CASE(64, 1, 0) HVD_CASE(64, 1, 1)
   HVD_CASE(128, 0, 0) HVD_CASE(128, 0, 1) HVD_CASE(128, 1, 0) HVD_CASE(128, 1, 1)
 #undef HVD_CASE
   return -4;
+}
+
+extern "C" int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int bn,
+                           int k_split, int epilogue, const float* bias, long long ldd, void* stream,
+                           unsigned lbo_a, unsigned sbo_a, unsigned lbo_b, unsigned sbo_b, const uint8_t* mask,
+                           float scale) {
+  return hvd_tc_gemm_ex(A, B, D, M, N, K, a_mn, b_mn, bn, k_split, epilogue, bias, ldd, stream, lbo_a, sbo_a, lbo_b,
+                        sbo_b, mask, scale, nullptr, nullptr);
 }

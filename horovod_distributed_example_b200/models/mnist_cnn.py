@@ -35,7 +35,7 @@ from ..keras import layers as L
 from ..keras import losses as losses_mod
 from ..ops import native
 from ..utils import nvtx
-from ..ops.gemm import EPI_ATOMIC_ADD, EPI_STORE, EPI_UNPOOL, tc_gemm
+from ..ops.gemm import EPI_ATOMIC_ADD, EPI_RS_PUSH, EPI_STORE, EPI_UNPOOL, tc_gemm
 
 
 def _declare(lib):
@@ -222,8 +222,20 @@ class MnistEngine:
         # 16) SMs are kept out of the dgrad/wgrad split and bucket 0 runs with two CTAs on each of them.
         # Measured: tail wins at 1 GPU (79.6 vs 87.7 us/step without a reservation) and at 2 GPUs (110 us/step
         # vs 134 / 115 with 16 / 24 SMs reserved), so tail is the default; overlap stays selectable.
-        mode = os.environ.get("HVD_BUCKET_MODE", "tail")
-        self._bucket_mode = mode if mode in ("tail", "overlap") else "tail"
+        # HVD_BUCKET_MODE=pipelined (default): no bucket kernels at all.  dense1's dW GEMM pushes its tiles to
+        # their owner ranks while the conv backward runs, ONE tail kernel does the barrier-free LL allreduce +
+        # update of the small tensors and the owners' reduce + update + store of the big one, and the next
+        # step's dense1 forward waits on a counter instead of anybody sitting in an exit barrier
+        # (parallel/pipeline.py).  Needs the 72 row tiles of dense_1/kernel to split evenly over the ranks.
+        from ..parallel import pipeline as pipe_mod
+        mode = os.environ.get("HVD_BUCKET_MODE", "pipelined")
+        if mode not in ("tail", "overlap", "pipelined"):
+            mode = "pipelined"
+        if mode == "pipelined" and (self.fused is None or not pipe_mod.supported(self.fused.ctx.size, 9216)
+                                    or self._debug_modes()):
+            mode = "tail"
+        self._bucket_mode = mode
+        self.pipe = None
         reserve = int(os.environ.get("HVD_RESERVE_SMS", 16)) if self._bucket_mode == "overlap" else 0
         d_def, w_def = (110, 38) if reserve == 0 else (max(148 - reserve - 32, 8), 32)
         self._dgrad_ctas = int(os.environ.get("HVD_DGRAD_CTAS", d_def))     # dgrad and wgrad run side by side: split the SMs
@@ -240,6 +252,19 @@ class MnistEngine:
             self.fused = opt._fused
             if reserve > 0 and not basics.state().config.comm_ctas:
                 self.fused.ctas[0] = min(self.fused.ctas[0], 2 * reserve)
+        if self._bucket_mode == "pipelined":
+            ar = model.arena
+            big = ar.spec(f"{self.names['f1']}/kernel")
+            w0, w1 = big.offset, big.offset + big.numel
+            self.pipe = pipe_mod.PipelinedStep(self.fused.ctx, self.fused.buf, self.fused.base_off, ar, opt.kind,
+                                               (0, w0), (w0, w1), (w1, ar.n),
+                                               ll_ctas=int(os.environ.get("HVD_LL_CTAS", 0)) or None,
+                                               ctas=int(os.environ.get("HVD_TAIL_CTAS", 0)) or None)
+            opt._pipe = self.pipe             # checkpoints gather the owner-sharded state through it
+            if os.environ.get("HVD_TAIL_TRACE", "0") == "1" or basics.state().timeline is not None:
+                self.pipe.enable_trace()
+        elif hasattr(opt, "_pipe"):
+            opt._pipe = None
         cfg = basics.state().config
         self._fault = cfg.parsed_fault() if cfg is not None else None
         self._debug = cfg is not None and bool(cfg.debug_checksum or cfg.debug_poison)
@@ -249,9 +274,25 @@ class MnistEngine:
         self.use_graph = os.environ.get("HVD_NO_GRAPH", "0") != "1" and self.fused is not None
         if self.fused is not None:
             opt._defer_push = True           # hyper-parameter rows are written at step start (see _run_step)
-        self.launches_per_step = (7 if self._fused_bwd else 8) + (len(self.fused.buckets) if self.fused is not None else 0)
+        if self.pipe is not None:      # tail kernel (+ the tile-flag kernel behind dense1's dW at size > 1)
+            comm_launches = 1 + (1 if (self.pipe.flag_kernel and self.pipe.n > 1) else 0)
+        else:
+            comm_launches = len(self.fused.buckets) if self.fused is not None else 0
+        self.launches_per_step = (7 if self._fused_bwd else 8) + comm_launches
 
     # ------------------------------------------------------------------ helpers
+    @staticmethod
+    def _debug_modes() -> bool:
+        """HVD_DEBUG_POISON NaN-fills the local gradient slab after each update, which the pipelined step's
+        big gradient never visits: those runs use the bucket kernels."""
+        cfg = basics.state().config
+        return cfg is not None and bool(cfg.debug_poison)
+
+    def describe_comm(self):
+        if self.pipe is not None:
+            return self.pipe.describe()
+        return self.fused.describe() if self.fused is not None else ["single process, unfused optimizer"]
+
     _GUARD_BYTES = 4096
 
     def _alloc(self, name, shape, dtype):
@@ -314,9 +355,10 @@ class MnistEngine:
 
     def _forward_dense(self, B: int):
         if "d1fwd" not in self._SKIP:
+            # pipelined mode: the first reader of dense_1/kernel waits until its owners' stores have landed
             tc_gemm(self.p2, self._p("f1", "kernel"), B, 128, 9216, a_mn=False, b_mn=True, bn=128,
                     k_split=int(os.environ.get('HVD_D1_KSPLIT', 32)), epilogue=EPI_ATOMIC_ADD, out=self.h_pre,
-                    stream=self._s())
+                    stream=self._s(), wait=self.pipe.param_wait() if self.pipe is not None else None)
 
     def _forward_conv(self, B: int, training: bool, which: Optional[int] = None):
         lib, s = self.lib, self._s()
@@ -370,6 +412,21 @@ class MnistEngine:
         self._forward_dense(B)
         self._head(B, True, True, which)
         self._ev_fork.record(main)
+        if self.pipe is not None:
+            # GEMM -> reduce-scatter in one kernel: every 128-row tile goes to its owner's receive area (local
+            # memory or a peer over NVLink).  On its own stream and joined only before the tail kernel, so its
+            # peer stores + system fence drain under dX and the conv backward instead of delaying them.
+            self.side.wait_event(self._ev_fork)
+            if "dw" not in self._SKIP:
+                with torch.cuda.stream(self.side):
+                    tc_gemm(self.p2, self.dh_pre, 9216, 128, B, a_mn=True, b_mn=True, bn=128, epilogue=EPI_RS_PUSH,
+                            out=None, stream=self.side.cuda_stream, rs=self.pipe.rs_push())
+                    self.pipe.launch_rs_flags(stream=self.side)
+            if "dx" not in self._SKIP:
+                tc_gemm(self.dh_pre, self._p("f1", "kernel"), B, 9216, 128, a_mn=False, b_mn=False, bn=64,
+                        epilogue=EPI_UNPOOL, out=self.dy2.view(-1, 64), mask=self.mask2, scale=1.0 / self.keep1,
+                        stream=self._s())
+            return
         self.side2.wait_event(self._ev_fork)
         with torch.cuda.stream(self.side2):
             if "dw" not in self._SKIP:
@@ -412,7 +469,11 @@ class MnistEngine:
                                               self._g("c1", "kernel", which).data_ptr(),
                                               self._g("c1", "bias", which).data_ptr()), "conv2_dgrad")
         main.wait_stream(self.side2)
-        if fused is not None and "b1" not in self._SKIP:
+        if self.pipe is not None:
+            main.wait_stream(self.side)          # dense1 dW (pushed to its owners) joins here
+            if "b1" not in self._SKIP:
+                self.pipe.launch_tail(which, which, self.m.optimizer.hyper_row(which).data_ptr())
+        elif fused is not None and "b1" not in self._SKIP:
             for i in range(1 if self._bucket_mode == "overlap" else 0, len(fused.buckets)):
                 fused.run_bucket(i, which, self._exit_barrier(), hyper_row=which)
 
@@ -423,6 +484,9 @@ class MnistEngine:
         """Make the current stream wait for any update still running on the side stream (call before
         anything outside the training step reads parameters or optimizer state)."""
         torch.cuda.current_stream(self.dev).wait_stream(self.side)
+        if self.pipe is not None:
+            # ... and for the weights that OTHER GPUs' tail kernels are still storing into this arena
+            self.pipe.launch_param_wait()
 
     def _stage_host(self, x, y):
         """Enqueue the H2D copy of one host batch into the input buffers of the NEXT step's parity on the
@@ -542,6 +606,7 @@ class MnistEngine:
             opt.iterations += 1
             self._parity ^= 1 if self.m.arena.n_grad_bufs == 2 else 0
             if self._debug:
+                self.sync_params()           # the replica checksum must see the weights peers are still sending
                 opt._debug_after_step(self.m.arena, which)
         self._train_steps += 1
         nvtx.pop()

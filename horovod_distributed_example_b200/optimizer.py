@@ -80,7 +80,10 @@ class _DistributedMixin:
 
     def materialize_state(self) -> None:
         """Gather sharded optimizer slots to this rank (before a checkpoint is written)."""
-        if self._fused is not None:
+        pipe = getattr(self, "_pipe", None)
+        if pipe is not None:
+            pipe.materialize_state()           # pipelined engine: the big kernel's state rows live with their owners
+        elif self._fused is not None:
             self._fused.materialize_state()
 
     def begin_step(self) -> None:

@@ -1,0 +1,235 @@
+"""Host side of the pipelined data-parallel step (``csrc/comm/pipeline.cuh``, ``pipeline_tail.cu``).
+
+What ``hvd.DistributedOptimizer`` (reference ``mnist_keras.py:87``, ``tensorflow2_keras_mnist.py:58``) turns
+into on the fused MNIST engine when the world size divides the 72 row tiles of the Dense(128) kernel:
+
+* the GEMM that produces that kernel's gradient (98% of the bytes) pushes each output tile into the receive
+  area of the rank that owns those rows while the conv backward is still running (``tc_gemm`` EPI_RS_PUSH);
+* ONE tail kernel per step does the rest: a barrier-free LL one-shot allreduce + update of the ~80 KB of small
+  tensors, and the owner's reduce + update + store-to-every-replica of its rows;
+* nobody waits in an exit barrier: the next step's first reader of the big weights waits on a counter.
+
+This object owns the symmetric receive buffers and fills the argument structs; the engine launches through it.
+It also works on an emulated context (``PeerContext.emulate(n)``: n ranks on one GPU, one cooperative launch
+of the tail kernel, one GEMM launch per rank) so the kernels can be tested on a single-GPU box.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from ..ops import native
+from . import peer as peer_mod
+from .peer import MAX_CTAS, MAX_RANKS, HvdCommCtx
+
+SLOT_RS_PUSH, SLOT_TAIL, SLOT_READY = 24, 25, 26
+TILE = 128 * 128
+
+
+class HvdRsPush(ctypes.Structure):
+    _fields_ = [("recv", ctypes.c_void_p * MAX_RANKS), ("pad", ctypes.c_void_p * MAX_RANKS),
+                ("epoch", ctypes.c_void_p), ("rank", ctypes.c_int), ("nranks", ctypes.c_int),
+                ("tiles_per_owner", ctypes.c_int), ("shard_elems", ctypes.c_longlong), ("send_flags", ctypes.c_int)]
+
+
+class HvdParamWait(ctypes.Structure):
+    _fields_ = [("counter", ctypes.c_void_p), ("target", ctypes.c_void_p), ("error", ctypes.c_void_p),
+                ("timeout_ns", ctypes.c_ulonglong)]
+
+
+class HvdTailArgs(ctypes.Structure):
+    _fields_ = [("a0", ctypes.c_longlong), ("a1", ctypes.c_longlong), ("b0", ctypes.c_longlong),
+                ("b1", ctypes.c_longlong), ("w0", ctypes.c_longlong), ("w1", ctypes.c_longlong),
+                ("grad_off", ctypes.c_longlong), ("param_off", ctypes.c_longlong),
+                ("slot0_off", ctypes.c_longlong), ("slot1_off", ctypes.c_longlong),
+                ("recv", ctypes.c_void_p * MAX_RANKS), ("ll", ctypes.c_void_p * MAX_RANKS),
+                ("ready_target", ctypes.c_void_p * MAX_RANKS), ("hyper", ctypes.c_void_p),
+                ("scale", ctypes.c_float), ("kind", ctypes.c_int), ("parity", ctypes.c_int),
+                ("ll_ctas", ctypes.c_int), ("use_mc", ctypes.c_int), ("trace", ctypes.c_void_p * MAX_RANKS)]
+
+
+def _declare(lib):
+    if getattr(lib, "_hvd_pipe_declared", False):
+        return
+    P = ctypes.POINTER
+    lib.hvd_tail_launch.restype = ctypes.c_int
+    lib.hvd_tail_launch.argtypes = [P(HvdCommCtx), P(HvdTailArgs), ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
+    lib.hvd_param_wait_launch.restype = ctypes.c_int
+    lib.hvd_param_wait_launch.argtypes = [P(HvdParamWait), ctypes.c_void_p]
+    lib.hvd_rs_flags_launch.restype = ctypes.c_int
+    lib.hvd_rs_flags_launch.argtypes = [P(HvdRsPush), ctypes.c_void_p]
+    lib._hvd_pipe_declared = True
+
+
+def supported(nranks: int, big_rows: int) -> bool:
+    """The big tensor's 128-row tiles must split evenly over the ranks."""
+    return big_rows % 128 == 0 and (big_rows // 128) % nranks == 0 and (big_rows // 128) <= MAX_CTAS
+
+
+class PipelinedStep:
+    """Buffers + argument structs for one model: ``small_a`` / ``small_b`` are the two element ranges of the
+    slab that hold the small tensors (in front of and behind the big one), ``big`` is the big tensor's range."""
+
+    def __init__(self, ctx: peer_mod.PeerContext, arena_buf: peer_mod.SymmBuffer, base_off: int, arena, kind: int,
+                 small_a, big, small_b, ll_ctas: Optional[int] = None, ctas: Optional[int] = None):
+        self.ctx, self.buf, self.base_off, self.arena, self.kind = ctx, arena_buf, base_off, arena, kind
+        self.lib = native.cuda_lib()
+        _declare(self.lib)
+        n = ctx.size
+        self.n = n
+        self.small_a, self.big, self.small_b = tuple(small_a), tuple(big), tuple(small_b)
+        w = self.big[1] - self.big[0]
+        if w % (TILE * n) != 0:
+            raise ValueError("the big tensor does not split into whole 128x128 tiles per rank")
+        self.shard = w // n
+        self.tiles_per_owner = self.shard // TILE
+        nsmall = (self.small_a[1] - self.small_a[0]) + (self.small_b[1] - self.small_b[0])
+        if nsmall % 4:
+            raise ValueError("small ranges must be multiples of 4 elements")
+        self.npk = nsmall // 2
+        # symmetric receive areas (collective allocations: same order on every rank)
+        self.rs = ctx.alloc(w * 4, multicast=False)                      # [src][shard] floats
+        self.ll = ctx.alloc(2 * n * self.npk * 16, multicast=False)      # [parity][src][packet] x 16 B
+        n_local = n if ctx.emulated else 1
+        self._targets = [torch.zeros(1, dtype=torch.int32, device=ctx.device) for _ in range(n_local)]
+        # One CTA per SM: 256-thread CTAs, the LL part wants one packet per thread, the rest stream the shard
+        self.ll_ctas = ll_ctas or max(1, min(64, (self.npk + 255) // 256))
+        total = ctas or 296                # two 256-thread CTAs per SM: the shard part is a bandwidth-bound stream
+        if ctx.emulated:
+            total = max(2, min(total, (148 * 2) // n))
+            self.ll_ctas = max(1, min(self.ll_ctas, total // 2))
+        self.ctas = max(total, self.ll_ctas + 1)
+        import os
+        self.flag_kernel = os.environ.get("HVD_RS_FLAG_KERNEL", "1") != "0"
+        self.use_mc = bool(arena_buf.mc_ptr) and n > 1 and os.environ.get("HVD_TAIL_MC", "1") != "0"
+        self._rs_cache = {}
+        self._wait = None
+        # device-side trace ring (64 steps x 16 globaltimer stamps) - HVD_TIMELINE on the engine path, profiling
+        self._trace = None
+
+    # ------------------------------------------------------------------ structs
+    def _rank_index(self, r: Optional[int]) -> int:
+        return (r if r is not None else 0) if self.ctx.emulated else 0
+
+    def rs_push(self, rank: Optional[int] = None) -> HvdRsPush:
+        """Descriptor for the producing GEMM of ``rank`` (emulation: pass the virtual rank)."""
+        key = rank if self.ctx.emulated else -1
+        s = self._rs_cache.get(key)
+        if s is None:
+            s = HvdRsPush()
+            for r in range(self.n):
+                s.recv[r] = self.rs.ptrs[r]
+                s.pad[r] = self.ctx.pad.ptrs[r]
+            s.epoch = self.ctx._epochs[self._rank_index(rank)].data_ptr()
+            s.rank = rank if self.ctx.emulated else self.ctx.rank
+            s.nranks = self.n
+            s.tiles_per_owner = self.tiles_per_owner
+            s.shard_elems = self.shard
+            s.send_flags = 0 if self.flag_kernel else 1
+            self._rs_cache[key] = s
+        return s
+
+    def launch_rs_flags(self, rank: Optional[int] = None, stream=None) -> None:
+        """Publish the tiles of the EPI_RS_PUSH GEMM just enqueued on ``stream`` (no-op when the GEMM's own CTAs
+        raise the flags, or at size 1)."""
+        if not self.flag_kernel or self.n == 1:
+            return
+        rc = self.lib.hvd_rs_flags_launch(ctypes.byref(self.rs_push(rank)), self.ctx._stream(stream))
+        if rc != 0:
+            raise RuntimeError(f"hvd_rs_flags_launch failed: {rc}")
+
+    def counter_ptr(self, rank: Optional[int] = None) -> int:
+        r = (rank or 0) if self.ctx.emulated else self.ctx.rank
+        return self.ctx.pad.ptrs[r] + 4 * ((SLOT_READY * MAX_CTAS) * MAX_RANKS)
+
+    def param_wait(self, rank: Optional[int] = None) -> Optional[HvdParamWait]:
+        """Wait descriptor for kernels that read the big weights (None at size 1: nothing arrives from peers)."""
+        if self.n == 1:
+            return None
+        if self.ctx.emulated or self._wait is None:
+            w = HvdParamWait()
+            w.counter = self.counter_ptr(rank)
+            w.target = self._targets[self._rank_index(rank)].data_ptr()
+            w.error = self.ctx._err.data_ptr()
+            w.timeout_ns = self.ctx.timeout_ns
+            if self.ctx.emulated:
+                return w
+            self._wait = w
+        return self._wait
+
+    def tail_args(self, grad_buf: int, parity: int, hyper_ptr: int) -> HvdTailArgs:
+        ar, a = self.arena, HvdTailArgs()
+        a.a0, a.a1 = self.small_a
+        a.b0, a.b1 = self.small_b
+        a.w0, a.w1 = self.big
+        a.grad_off = self.base_off + ar.grad_offset(grad_buf)
+        a.param_off = self.base_off + ar.param_offset
+        a.slot0_off = self.base_off + (ar.slot_offset(0) if ar.n_slots > 0 else 0)
+        a.slot1_off = self.base_off + (ar.slot_offset(1) if ar.n_slots > 1 else 0)
+        for r in range(self.n):
+            a.recv[r] = self.rs.ptrs[r]
+            a.ll[r] = self.ll.ptrs[r]
+            a.ready_target[r] = self._targets[self._rank_index(r)].data_ptr()
+            a.trace[r] = self._trace[self._rank_index(r)].data_ptr() if self._trace is not None else None
+        a.hyper = hyper_ptr
+        a.scale = 1.0 / self.n
+        a.kind, a.parity, a.ll_ctas, a.use_mc = self.kind, parity & 1, self.ll_ctas, int(self.use_mc)
+        return a
+
+    def enable_trace(self) -> None:
+        """Must be called before the step is captured into a CUDA graph (the pointer is a kernel argument)."""
+        if self._trace is None:
+            n_local = self.n if self.ctx.emulated else 1
+            self._trace = [torch.zeros(64, 16, dtype=torch.int64, device=self.ctx.device) for _ in range(n_local)]
+
+    def read_trace(self, rank: int = 0) -> torch.Tensor:
+        """[64][16] int64 nanosecond stamps (rows indexed by step epoch & 63); synchronizes the device."""
+        torch.cuda.synchronize(self.ctx.device)
+        return self._trace[self._rank_index(rank)].cpu()
+
+    # ------------------------------------------------------------------ launches
+    def launch_tail(self, grad_buf: int, parity: int, hyper_ptr: int, stream=None) -> None:
+        a = self.tail_args(grad_buf, parity, hyper_ptr)
+        rc = self.lib.hvd_tail_launch(ctypes.byref(self.ctx.comm_ctx(self.buf)), ctypes.byref(a), self.ctas,
+                                      self.ctx._stream(stream), self.n if self.ctx.emulated else 0)
+        if rc != 0:
+            msg = self.lib.hvd_cuda_error_string(rc).decode() if rc > 0 else f"bad arguments ({rc})"
+            raise RuntimeError(f"hvd_tail_launch failed: {msg}")
+
+    def launch_param_wait(self, stream=None) -> None:
+        """Make ``stream`` wait until every weight the peers' last tail kernels sent has landed in this arena."""
+        w = self.param_wait()
+        if w is None:
+            return
+        rc = self.lib.hvd_param_wait_launch(ctypes.byref(w), self.ctx._stream(stream))
+        if rc != 0:
+            raise RuntimeError(f"hvd_param_wait_launch failed: {rc}")
+
+    def shard_range(self, rank: int):
+        """Element range of the slab whose parameters AND optimizer state rank ``rank`` owns."""
+        s = self.big[0] + rank * self.shard
+        return s, s + self.shard
+
+    def materialize_state(self) -> None:
+        """Pull the optimizer-state rows owned by the other ranks into this rank's arena (one-sided peer
+        reads; called before a checkpoint is written).  The caller has already waited on the ready counter,
+        which every owner bumps only after its state writes are visible."""
+        ar = self.arena
+        me = 0 if self.ctx.emulated else self.ctx.rank
+        for r in range(self.n):
+            if r == me:
+                continue
+            s, e = self.shard_range(r)
+            for k in range(ar.n_slots):
+                self.ctx.pull(self.buf, r, self.base_off + ar.slot_offset(k) + s, e - s)
+        torch.cuda.synchronize(ar.device)
+
+    def describe(self):
+        w = (self.big[1] - self.big[0]) * 4
+        sm = self.npk * 8
+        st = "multimem.st" if self.use_mc else "peer stores"
+        return [f"big[{self.big[0]}:{self.big[1]}] {w}B: dW GEMM epilogue pushes tiles to their owner (reduce-scatter), "
+                f"owner update, {st} to every replica, deferred ready-counter wait; shard ctas={self.ctas - self.ll_ctas}",
+                f"small {sm}B: LL one-shot (flagged 16B packets, no barrier), ll ctas={self.ll_ctas}"]
