@@ -35,12 +35,13 @@ def main():
     hvd.barrier()
     tr = be.pipe.read_trace().numpy().astype(np.int64)
     order = np.argsort(tr[:, 0])
-    tr = tr[order][-48:]
-    rel = lambda k, b: float(np.mean(tr[:, k] - tr[:, b])) / 1e3
+    tr = tr[order][-49:-1]                  # (the newest row has no all-gather / next-step stamps yet)
+    rel = lambda k, b: float(np.median(tr[:, k] - tr[:, b])) / 1e3
     out = {"rank": hvd.rank(), "n": hvd.size(),
            "ll_pushed": rel(1, 0), "ll_all_arrived": rel(2, 0), "ll_done": rel(3, 0),
-           "shard_entry_vs_ll_entry": rel(4, 0), "shard_tiles_there": rel(5, 4), "shard_peers_entered": rel(6, 4),
-           "shard_stores_issued": rel(8, 4), "shard_fence_done": rel(9, 4), "shard_published": rel(7, 4), "step_period": float(np.mean(np.diff(tr[:, 0]))) / 1e3,
+           "shard_entry_vs_ll_entry": rel(4, 0), "shard_tiles_there": rel(5, 4), "shard_done": rel(7, 4),
+           "ag_start_after_tail_entry": rel(10, 0), "ag_flags_after_tail_entry": rel(11, 0),
+           "d1fwd_wait_begin_after_tail_entry": rel(12, 0), "d1fwd_wait_us": rel(13, 12), "step_period": float(np.median(np.diff(tr[:, 0]))) / 1e3,
            "entry_abs_last": int(tr[-1, 0])}
     allo = hvd.allgather_object(out)
     if hvd.rank() == 0:

@@ -15,15 +15,21 @@
 //   shard CTAs (blockIdx.x >= ll_ctas)  rank r owns rows [r*R/N, (r+1)*R/N) of the big kernel.  Its receive
 //              area holds one slot per source rank, filled by the producing GEMMs.  Wait for the per-tile
 //              flags (long since raised), sum the slots in fixed rank order, scale, update the owned rows of
-//              the parameters and of the optimizer state (state is sharded by owner), then - once every
-//              peer has entered ITS tail kernel, i.e. finished reading the old weights - store the new
-//              weights into every replica (multimem.st through the switch, or one peer store per rank) and
-//              bump every rank's "ready" counter with release semantics.  Nobody waits for those stores
-//              here: the next step's first reader of the weights (tc_gemm wait hook) checks the counter.
+//              this rank's parameters and of the optimizer state (state is sharded by owner).  Purely local
+//              traffic, 1/N of the full update.
+//
+// hvd_allgather_kernel delivers the updated rows to the other replicas.  It is NOT part of the tail: a handful
+// of 128-thread, 32-register CTAs enqueued at the start of the next step (or by a host-side flush) that fit on
+// the SMs next to the conv forward CTAs, copy the owned rows into every peer's arena (multimem.st through the
+// switch, or one peer store per rank) and stamp a version flag on every peer.  The 4+ MB that every GPU receives
+// per step therefore crosses NVLink while the conv forward computes, and the first reader of the big weights
+// (tc_gemm wait hook) checks the flags - nobody waits in an exit barrier and no kernel on the critical path sits
+// through the acknowledgement of its peer stores (measured: 5 us at 2 ranks, 9 us at 8 when it was in the tail).
 //
 // Capability parity: the allreduce + 1/N + optimizer step of hvd.DistributedOptimizer (reference
 // mnist_keras.py:84-87, tensorflow2_keras_mnist.py:55-58).
 #include "pipeline.cuh"
+#include "kernels/tc_common.cuh"
 
 #include <cooperative_groups.h>
 #include <string.h>
@@ -40,15 +46,14 @@ struct HvdTailArgs {
   float* recv[HVD_MAX_RANKS];     // recv[r]: rank r's receive area of the reduce-scatter, [src][shard]; only
                                   // [own rank] is read (the array form lets one emulated launch carry all ranks)
   float4* ll[HVD_MAX_RANKS];      // ll[r]: rank r's LL receive buffer as mapped here: [parity][src][packets]
-  uint32_t* ready_target[HVD_MAX_RANKS];   // [own rank]: device word = counter value meaning "every weight of the
-                                  // last step has landed here"
+  uint32_t* version[HVD_MAX_RANKS];        // [own rank]: device word = number of updates applied to the big tensor
+                                  // (written here, stamped on the peers by the all-gather, awaited by readers)
   const float* hyper;             // device fp32[8]
   float scale;                    // 1/N
   int kind, parity, ll_ctas, use_mc;
   // HVD_TIMELINE / profiling: ring of 64 records x 16 %globaltimer stamps (ns), indexed by epoch & 63, or null.
   //   [0] LL CTA 0 entered   [1] LL CTA 0 pushed its packets   [2] LL CTA 0 has every peer's packets   [3] LL CTA 0 done
-  //   [4] first shard CTA entered  [5] its tiles were there  [6] peers had entered (stores may start)  [7] it published
-  //   [8] its last store was issued  [9] its system fence returned
+  //   [4] first shard CTA entered  [5] its tiles were there  [7] it is done   ([10], [11]: hvd_allgather_kernel)
   unsigned long long* trace[HVD_MAX_RANKS];
 };
 
@@ -119,10 +124,6 @@ __global__ void __launch_bounds__(256, 2) hvd_tail_kernel(HvdCommCtx c, HvdTailA
 
   if ((int)blockIdx.x < a.ll_ctas) {
     // ------------------------------------------------------------------ small tensors: LL one-shot
-    // "I am in my tail": my reads of the old big weights are done.  Sent by the last warp of the last LL CTA so the
-    // release's system fence does not sit in front of a warp that has packets to push.
-    if ((int)blockIdx.x == a.ll_ctas - 1 && tid >= 224 && tid - 224 < N && tid - 224 != rank)
-      st_release_sys(hvd_flag(c, tid - 224, HVD_SLOT_TAIL, 0, rank), ep);
     const long long na = a.a1 - a.a0, nsmall = na + (a.b1 - a.b0);
     const long long npk = nsmall / 2;                     // packets of two floats (ranges are multiples of 4)
     const uint32_t fl = ep;
@@ -213,8 +214,6 @@ __global__ void __launch_bounds__(256, 2) hvd_tail_kernel(HvdCommCtx c, HvdTailA
     const long long el0 = a.w0 + (long long)rank * shard;   // first owned element in the slab
     const float* recv = a.recv[rank];
     constexpr int U = 2;
-    bool entered = (N == 1);
-    // the trip count is the same for every thread of the CTA (there is a __syncthreads inside)
     for (long long base = i0; base < i1; base += (long long)blockDim.x * U) {
       const long long i = base + tid;
       float4 pv[U], s0v[U], s1v[U], acc[U];
@@ -254,58 +253,133 @@ __global__ void __launch_bounds__(256, 2) hvd_tail_kernel(HvdCommCtx c, HvdTailA
         *reinterpret_cast<float4*>(mine + a.slot0_off + el) = s0v[u];
         if (KIND != HVD_KIND_SGD) *reinterpret_cast<float4*>(mine + a.slot1_off + el) = s1v[u];
       }
-      if (!entered) {
-        // The new weights may only land in a peer's arena after that peer finished every read of the old
-        // ones (its Dense backward): it says so when its own tail kernel starts.  Everything above overlapped
-        // that wait.
-        if (tid < N && tid != rank && !tail_wait_flag(c, hvd_flag(c, rank, HVD_SLOT_TAIL, 0, tid), ep, HVD_SLOT_TAIL, tid))
-          s_fail = 1;
-        __syncthreads();
-        if (s_fail) return;
-        entered = true;
-        if (tr_sh) tr[6] = globaltimer_ns();
-      }
+      // the owner's own replica; the other replicas get these rows from hvd_allgather_kernel
       const long long dst_base = (KIND == HVD_KIND_NONE) ? a.grad_off : a.param_off;
 #pragma unroll
       for (int u = 0; u < U; u++) {
         const long long idx = i + (long long)u * blockDim.x;
-        if (idx >= i1) continue;
-        const long long off = dst_base + el0 + idx * 4;
-        if (a.use_mc) {
-          multimem_st_f4(c.mc_base + off, res[u]);
-        } else {
-#pragma unroll
-          for (int r = 0; r < NR; r++)
-            if (r < N) {
-              if (r == rank) *reinterpret_cast<float4*>(mine + off) = res[u];
-              else st_sys_f4(c.base[r] + off, res[u]);
-            }
-        }
+        if (idx < i1) *reinterpret_cast<float4*>(mine + dst_base + el0 + idx * 4) = res[u];
       }
     }
-    if (tr_sh) tr[8] = globaltimer_ns();
-    if (N > 1) {
-      // publish: every store of this CTA is visible system-wide before any rank's counter moves.  The CTA barrier
-      // orders all threads' stores before the release of the few threads that signal (release is cumulative), so
-      // ONE system fence per signalling thread replaces a fence in each of the 256 threads (measured: 7 us + 3.5 us
-      // with per-thread fences at 2 ranks).
-      __syncthreads();
-      if (tr_sh) tr[9] = globaltimer_ns();
-      if (tid < N) red_release_sys_add(hvd_flag(c, tid, HVD_SLOT_READY, 0, 0), 1u);
-    }
     if (tr_sh) tr[7] = globaltimer_ns();
-    if (d == 0 && tid == 0 && N > 1) *a.ready_target[rank] += (uint32_t)(N * D);   // read by the next kernels on this GPU
+    if (d == 0 && tid == 0) *a.version[rank] = ep;          // read by the all-gather / the readers' wait (stream order)
   }
   if (tr_ll) tr[3] = globaltimer_ns();
   hvd_epoch_store(c, HVD_SLOT_TAIL, ep);
 }
 
-// Spin (one thread) until this rank's "ready" counter reaches the published target: every weight the peers'
-// tail kernels stored into this arena has landed.  Enqueued by the host before it reads parameters outside a
-// training step (checkpoint, evaluate, get_weights) - a stream synchronize alone does not cover stores that
-// OTHER GPUs are still sending.
-__global__ void hvd_param_wait_kernel(HvdParamWait w) {
-  if (threadIdx.x == 0) hvd_param_wait(w);
+// Wait (one warp) until every peer has delivered the current version of its rows into this arena.  Enqueued
+// by the host before it reads parameters outside a training step (checkpoint, evaluate, get_weights) - a stream
+// synchronize alone does not cover stores that OTHER GPUs are still sending.
+__global__ void hvd_param_wait_kernel(HvdParamWait w) { hvd_param_wait_warp(w); }
+
+struct HvdAllgatherArgs {
+  long long w0, w1;               // the big tensor's range in the slab
+  long long param_off;            // slab offset of the parameters inside the arena buffer
+  const uint32_t* version[HVD_MAX_RANKS];   // [own rank]: device word written by the tail kernel
+  int use_mc;
+  unsigned long long* trace[HVD_MAX_RANKS];  // same ring as the tail's: [10] CTA 0 started, [11] CTA 0 stamped its flags
+};
+
+// Deliver this rank's rows of the big tensor to every other replica and stamp the version on every peer.
+// 128 threads, <= 32 registers: 4 K registers per CTA, which is what an SM has left beside a conv2 forward CTA.
+__global__ void __launch_bounds__(128, 16) hvd_allgather_kernel(HvdCommCtx c, HvdAllgatherArgs a) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int rank = hvd_rank(c), N = c.nranks, tid = threadIdx.x;
+  const uint32_t v = *a.version[rank];
+  unsigned long long* tr = (a.trace[rank] && blockIdx.x == 0 && tid == 0) ? a.trace[rank] + (size_t)(v & 63) * 16 : nullptr;
+  if (tr) tr[10] = globaltimer_ns();
+  const long long shard = (a.w1 - a.w0) / N;
+  const long long n4 = shard / 4;
+  const long long per = (n4 + gridDim.x - 1) / gridDim.x;
+  const long long i0 = (long long)blockIdx.x * per, i1 = i0 + per < n4 ? i0 + per : n4;
+  const long long off = a.param_off + a.w0 + (long long)rank * shard;
+  const float* src = c.base[rank] + off;
+  __shared__ float* peer[HVD_MAX_RANKS];       // shared memory, not registers: the kernel lives on 32 registers
+  if (tid < HVD_MAX_RANKS) peer[tid] = c.base[tid];
+  __syncthreads();
+  for (long long i = i0 + tid; i < i1; i += 4 * 128) {
+    float4 q[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (i + u * 128 < i1) q[u] = ld_f4(src + (i + u * 128) * 4);
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      if (i + u * 128 >= i1) continue;
+      const long long o = off + (i + u * 128) * 4;
+      if (a.use_mc) {
+        multimem_st_f4(c.mc_base + o, q[u]);          // also rewrites this rank's own copy with the same bits
+      } else {
+        for (int r = 0; r < N; r++)
+          if (r != rank) st_sys_f4(peer[r] + o, q[u]);
+      }
+    }
+  }
+  // every thread's stores happen-before the barrier; the release of the signalling threads is cumulative
+  __syncthreads();
+  if (tid < N && tid != rank) st_release_sys(hvd_flag(c, tid, HVD_SLOT_READY, blockIdx.x, rank), v);
+  if (tr) tr[11] = globaltimer_ns();
+}
+
+// The same delivery with the TMA engine doing the copying: ONE WARP per CTA, one lane issuing bulk copies
+// (cp.async.bulk global -> shared -> every peer's arena) through a ring of 16 KB shared-memory buffers.  No
+// registers to speak of, no load latency to cover with threads: the version above needs thousands of threads to
+// keep enough 16-byte loads in flight and took 9 us alone / 20-40 us squeezed in beside the conv forward CTAs
+// with the 8 K threads that fit there; here a few dozen warps keep several hundred KB in flight.
+constexpr int AG_CHUNK = 16384;
+constexpr int AG_NBUF = 3;
+
+__global__ void __launch_bounds__(32) hvd_allgather_tma_kernel(HvdCommCtx c, HvdAllgatherArgs a) {
+  extern __shared__ __align__(128) uint8_t ag_smem[];
+  __shared__ __align__(8) uint64_t full[AG_NBUF];
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int rank = hvd_rank(c), N = c.nranks, lane = threadIdx.x;
+  const uint32_t v = *a.version[rank];
+  unsigned long long* tr = (a.trace[rank] && blockIdx.x == 0 && lane == 0) ? a.trace[rank] + (size_t)(v & 63) * 16 : nullptr;
+  if (tr) tr[10] = globaltimer_ns();
+  const long long shard_bytes = (a.w1 - a.w0) / N * 4;
+  long long per = (shard_bytes + gridDim.x - 1) / gridDim.x;
+  per = (per + 127) / 128 * 128;
+  const long long b0 = (long long)blockIdx.x * per;
+  const long long b1 = b0 + per < shard_bytes ? b0 + per : shard_bytes;
+  const long long off = (a.param_off + a.w0) * 4 + (long long)rank * shard_bytes;      // byte offset in the arena buffer
+  if (lane == 0) {
+    for (int i = 0; i < AG_NBUF; i++) tc::mbar_init(&full[i], 1);
+    tc::fence_barrier_init();
+    const int nchunk = b1 > b0 ? (int)((b1 - b0 + AG_CHUNK - 1) / AG_CHUNK) : 0;
+    const char* src = reinterpret_cast<const char*>(c.base[rank]) + off;
+    auto load = [&](int k) {
+      const long long o = b0 + (long long)k * AG_CHUNK;
+      const uint32_t bytes = (uint32_t)((b1 - o) < AG_CHUNK ? (b1 - o) : AG_CHUNK);
+      uint64_t* bar = &full[k % AG_NBUF];
+      tc::mbar_expect_tx(bar, bytes);
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(tc::smem_u32(ag_smem + (k % AG_NBUF) * AG_CHUNK)), "l"(src + o), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
+    };
+    for (int k = 0; k < AG_NBUF - 1 && k < nchunk; k++) load(k);
+    for (int k = 0; k < nchunk; k++) {
+      tc::mbar_wait(&full[k % AG_NBUF], (k / AG_NBUF) & 1);
+      const long long o = b0 + (long long)k * AG_CHUNK;
+      const uint32_t bytes = (uint32_t)((b1 - o) < AG_CHUNK ? (b1 - o) : AG_CHUNK);
+      for (int r = 0; r < N; r++) {
+        if (r == rank) continue;
+        char* dst = reinterpret_cast<char*>(c.base[r]) + off + o;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     ::"l"(dst), "r"(tc::smem_u32(ag_smem + (k % AG_NBUF) * AG_CHUNK)), "r"(bytes) : "memory");
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      if (k + AG_NBUF - 1 < nchunk) {
+        // the buffer chunk k-1 was sent from is the one chunk k+NBUF-1 lands in: its stores must have read it
+        asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        load(k + AG_NBUF - 1);
+      }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // every peer store of this CTA is complete ...
+    asm volatile("fence.proxy.async;" ::: "memory");               // ... and ordered before the generic-proxy flag stores
+  }
+  __syncwarp();
+  if (lane < N && lane != rank) st_release_sys(hvd_flag(c, lane, HVD_SLOT_READY, blockIdx.x, rank), v);
+  if (tr) tr[11] = globaltimer_ns();
 }
 
 // Raise the "tile has landed" flags of a finished EPI_RS_PUSH GEMM (HvdRsPush.send_flags == 0): launched right
@@ -363,7 +437,6 @@ extern "C" int hvd_tail_launch(const HvdCommCtx* c, const HvdTailArgs* a, int ct
   if (ctas < 2 || ctas > HVD_MAX_CTAS || a->ll_ctas < 1 || a->ll_ctas >= ctas) return -2;
   if ((a->a0 | a->a1 | a->b0 | a->b1 | a->w0 | a->w1 | a->grad_off | a->param_off | a->slot0_off | a->slot1_off) & 3) return -3;
   if ((a->w1 - a->w0) % (4 * c->nranks) != 0 || ((a->w1 - a->w0) / c->nranks) % (128 * 128) != 0) return -4;
-  if (a->use_mc && c->mc_base == nullptr) return -5;
   cudaStream_t st = (cudaStream_t)stream;
   const int emu = emulate_ranks;
   cudaError_t e;
@@ -381,4 +454,38 @@ extern "C" int hvd_param_wait_launch(const HvdParamWait* w, void* stream) {
   if (!w) return -1;
   hvd_param_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*w);
   return (int)cudaGetLastError();
+}
+
+// emulate_ranks > 0: grid.y = rank (a plain launch: the kernel waits for nobody).
+// use_tma: the bulk-copy kernel (peer stores only; ignores a->use_mc).
+extern "C" int hvd_allgather_launch(const HvdCommCtx* c, const HvdAllgatherArgs* a, int ctas, void* stream,
+                                    int emulate_ranks, int use_tma) {
+  if (!c || !a || c->nranks < 2 || c->nranks > HVD_MAX_RANKS || ctas < 1 || ctas > HVD_MAX_CTAS) return -1;
+  if ((a->w0 | a->w1 | a->param_off) & 3 || (a->w1 - a->w0) % (4 * c->nranks) != 0) return -2;
+  if (a->use_mc && c->mc_base == nullptr) return -3;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(ctas, emulate_ranks > 0 ? emulate_ranks : 1); cfg.blockDim = dim3(128); cfg.stream = (cudaStream_t)stream;
+  // Highest priority: CTAs are dispatched grid by grid in submission order within a priority level, so without it
+  // these CTAs queue behind the conv forward kernels' not-yet-resident CTAs instead of slipping into the free
+  // thread slots beside them (measured: the copy started 7 us late and took 30 us).  Kept by graph capture.
+  int lo = 0, hi = 0;
+  cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributePriority;
+  at[0].val.priority = hi;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  if (use_tma) {
+    constexpr int smem = AG_NBUF * AG_CHUNK;
+    static tc::PerDeviceOnce attr;
+    if (attr.need()) {
+      if (cudaFuncSetAttribute(hvd_allgather_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -10;
+      attr.mark();
+    }
+    cfg.blockDim = dim3(32);
+    cfg.dynamicSmemBytes = smem;
+    return (int)cudaLaunchKernelEx(&cfg, hvd_allgather_tma_kernel, *c, *a);
+  }
+  return (int)cudaLaunchKernelEx(&cfg, hvd_allgather_kernel, *c, *a);
 }

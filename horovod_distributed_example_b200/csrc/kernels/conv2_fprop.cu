@@ -18,6 +18,7 @@
 // 16 epilogue warps in two sets.  Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of
 // tile i+1.  The epilogue writes only the pooled, dropped-out activations (4.7 MB instead of the
 // 18.9 MB conv output) plus one mask byte per element (arg-max + keep) for backward.
+#include "comm/pipeline.cuh"
 #include "mnist_common.cuh"
 #include "tc_common.cuh"
 
@@ -41,6 +42,11 @@ struct Params {
   float* p2;                                // [B, 12, 12, 64]
   uint8_t* mask;                            // [B, 12, 12, 64]
   const StepState* st;
+  // Pipelined data-parallel step: the spare warp of CTA 0 waits here until every peer has delivered its rows of
+  // dense_1/kernel (comm/pipeline.cuh).  This kernel does not read those weights - the wait rides along because
+  // it costs several microseconds of system-scope polling and fencing that would otherwise sit in front of the
+  // Dense forward; the kernel boundary orders the Dense forward's reads after it.
+  HvdParamWait wait;
 };
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -90,6 +96,8 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
       }
     }
+  } else if (warp == 3) {
+    if (blockIdx.x == 0) hvd_param_wait_warp(p.wait);
   } else if (warp == 1) {
     if (tc::elect_one()) {
       constexpr uint32_t idesc = tc::make_idesc_tf32(128, 64, 0, 1);
@@ -204,8 +212,9 @@ conv2_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
 // a1: [B,26,26,32] fp32 (conv1 output, post-relu); w2: HWIO [3,3,32,64]; bias2[64];
 // p2: [B,12,12,64]; mask: [B,12,12,64] bytes.  Returns 0 or a CUDA/driver error code.
-extern "C" int hvd_conv2_fprop(const float* a1, const float* w2, const float* bias2, float* p2, uint8_t* mask,
-                               const void* step_state, int B, int training, float keep, int ctas, void* stream) {
+extern "C" int hvd_conv2_fprop_ex(const float* a1, const float* w2, const float* bias2, float* p2, uint8_t* mask,
+                                  const void* step_state, int B, int training, float keep, int ctas, void* stream,
+                                  const HvdParamWait* wait) {
   CUtensorMap tmA, tmW;
   {
     uint64_t dims[4] = {32, 26, 26, (uint64_t)B};
@@ -225,7 +234,14 @@ extern "C" int hvd_conv2_fprop(const float* a1, const float* w2, const float* bi
   Params p;
   p.B = B; p.n_tiles = ((B + 1) / 2) * 9; p.training = training; p.keep = keep; p.bias = bias2; p.p2 = p2; p.mask = mask;
   p.st = reinterpret_cast<const mnist::StepState*>(step_state);
+  memset(&p.wait, 0, sizeof(p.wait));
+  if (wait) p.wait = *wait;
   if (ctas <= 0) ctas = 148;
   if (ctas > p.n_tiles) ctas = p.n_tiles;
   return (int)tc::launch_pdl(conv2_fprop_kernel, dim3(ctas), dim3(THREADS), SMEM_BYTES, (cudaStream_t)stream, tmA, tmW, p);
+}
+
+extern "C" int hvd_conv2_fprop(const float* a1, const float* w2, const float* bias2, float* p2, uint8_t* mask,
+                               const void* step_state, int B, int training, float keep, int ctas, void* stream) {
+  return hvd_conv2_fprop_ex(a1, w2, bias2, p2, mask, step_state, B, training, keep, ctas, stream, nullptr);
 }

@@ -266,14 +266,23 @@ __global__ void __launch_bounds__(256) colsum64_kernel(const float* __restrict__
 
 }  // namespace
 
-extern "C" int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a,
-                             int n_a, float* zero_b, int n_b, void* step_state, int advance_step, void* stream) {
+// blocks_per_sm (1..8): resident 256-thread CTAs per SM the grid is sized for.  8 fills every thread slot; the
+// pipelined multi-GPU step passes 7 so that the small all-gather CTAs enqueued beside it find a slot at once.
+extern "C" int hvd_conv1_fwd_ex(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a,
+                                int n_a, float* zero_b, int n_b, void* step_state, int advance_step, void* stream,
+                                int blocks_per_sm) {
   if ((n_a | n_b) & 3) return -1;
+  if (blocks_per_sm < 1 || blocks_per_sm > 8) return -2;
   const long long total = (long long)B * mnist::H1 * mnist::H1 * 4;
   int blocks = (int)((total + 255) / 256);
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > 148 * blocks_per_sm) blocks = 148 * blocks_per_sm;
   Conv1Prologue pro{zero_a, zero_a ? n_a : 0, zero_b, zero_b ? n_b : 0, reinterpret_cast<mnist::StepState*>(step_state), advance_step};
   return (int)tc::launch_pdl(conv1_fwd_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, w, bias, a1, B, pro);
+}
+
+extern "C" int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a,
+                             int n_a, float* zero_b, int n_b, void* step_state, int advance_step, void* stream) {
+  return hvd_conv1_fwd_ex(x, w, bias, a1, B, zero_a, n_a, zero_b, n_b, step_state, advance_step, stream, 8);
 }
 
 extern "C" int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels,

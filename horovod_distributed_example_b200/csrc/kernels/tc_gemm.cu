@@ -19,9 +19,9 @@
 //   EPI_RS_PUSH : the epilogue stages the 128 x 128 tile in shared memory and writes it, as whole 512-byte
 //                 rows, into the receive area of the rank that owns those weight rows - local memory or a peer
 //                 GPU over NVLink - then raises a per-tile flag there (GEMM -> reduce-scatter in one kernel);
-//   wait        : the TMA producer first waits until the weights it is about to read have been delivered by
-//                 their owners (a counter the previous step's tail kernels bump), instead of those kernels
-//                 sitting in an exit barrier.
+//   wait        : the TMA producer warp first waits until the weights it is about to read have been delivered by
+//                 their owners (version flags stamped by the all-gather CTAs that run beside the conv forward),
+//                 instead of anybody sitting in an exit barrier.
 #include "comm/pipeline.cuh"
 #include "tc_common.cuh"
 
@@ -48,7 +48,7 @@ struct GemmParams {
   const uint8_t* mask;                   // EPI_UNPOOL
   float scale;                           // EPI_UNPOOL: 1/keep
   HvdRsPush rs;                          // EPI_RS_PUSH
-  HvdParamWait wait;                     // counter == nullptr: no wait
+  HvdParamWait wait;                     // flags == nullptr: no wait
 };
 
 template <int BN>
@@ -98,8 +98,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc::pdl_wait();                       // everything above overlapped the previous kernel's tail
 
   if (warp == 0) {
+    hvd_param_wait_warp(p.wait);        // all 32 lanes poll the delivery flags in parallel
     if (tc::elect_one()) {
-      hvd_param_wait(p.wait);
       for (int i = 0; i < nkb; i++) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;

@@ -366,6 +366,8 @@ class Model:
                 lv, av = hh.result()
                 loss_h += lv * nn
                 acc_h += av * nn
+            if hasattr(be, "flush_params"):
+                be.flush_params()        # every rank: rows it owns reach the other replicas even if training stops here
             elogs = {"loss": (loss_h if asynchronous else float(loss_sum)) / max(seen, 1)}
             if self._metric_accuracy:
                 elogs["accuracy"] = (acc_h if asynchronous else float(acc_sum)) / max(seen, 1)

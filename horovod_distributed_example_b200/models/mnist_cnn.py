@@ -44,6 +44,10 @@ def _declare(lib):
     vp, ci, cf = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
     lib.hvd_conv1_fwd.restype = ci
     lib.hvd_conv1_fwd.argtypes = [vp, vp, vp, vp, ci, vp, ci, vp, ci, vp, ci, vp]
+    lib.hvd_conv1_fwd_ex.restype = ci
+    lib.hvd_conv1_fwd_ex.argtypes = [vp, vp, vp, vp, ci, vp, ci, vp, ci, vp, ci, vp, ci]
+    lib.hvd_conv2_fprop_ex.restype = ci
+    lib.hvd_conv2_fprop_ex.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, cf, ci, vp, vp]
     lib.hvd_conv2_fprop.restype = ci
     lib.hvd_conv2_fprop.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, cf, ci, vp]
     lib.hvd_head.restype = ci
@@ -208,6 +212,10 @@ class MnistEngine:
         self.state_f = self.state.view(torch.float32)
         self._graphs = {}
         self._parity = 0
+        self._ag_pending = False
+        self._conv1_bps = 8
+        self._ag_where = os.environ.get("HVD_AG_WHERE", "start")
+        self._wait_in = os.environ.get("HVD_WAIT_IN", "fprop")
         self.side = torch.cuda.Stream(device=dev)
         self.side2 = torch.cuda.Stream(device=dev)
         self._ev_fork = torch.cuda.Event()
@@ -259,8 +267,11 @@ class MnistEngine:
             self.pipe = pipe_mod.PipelinedStep(self.fused.ctx, self.fused.buf, self.fused.base_off, ar, opt.kind,
                                                (0, w0), (w0, w1), (w1, ar.n),
                                                ll_ctas=int(os.environ.get("HVD_LL_CTAS", 0)) or None,
-                                               ctas=int(os.environ.get("HVD_TAIL_CTAS", 0)) or None)
+                                               ctas=int(os.environ.get("HVD_TAIL_CTAS", 0)) or None,
+                                               ag_ctas=int(os.environ.get("HVD_AG_CTAS", 0)) or None)
             opt._pipe = self.pipe             # checkpoints gather the owner-sharded state through it
+            if self.pipe.n > 1:               # leave thread slots for the all-gather CTAs that start with conv1
+                self._conv1_bps = int(os.environ.get("HVD_CONV1_BPS", 7))
             if os.environ.get("HVD_TAIL_TRACE", "0") == "1" or basics.state().timeline is not None:
                 self.pipe.enable_trace()
         elif hasattr(opt, "_pipe"):
@@ -358,7 +369,8 @@ class MnistEngine:
             # pipelined mode: the first reader of dense_1/kernel waits until its owners' stores have landed
             tc_gemm(self.p2, self._p("f1", "kernel"), B, 128, 9216, a_mn=False, b_mn=True, bn=128,
                     k_split=int(os.environ.get('HVD_D1_KSPLIT', 32)), epilogue=EPI_ATOMIC_ADD, out=self.h_pre,
-                    stream=self._s(), wait=self.pipe.param_wait() if self.pipe is not None else None)
+                    stream=self._s(),
+                    wait=self.pipe.param_wait() if (self.pipe is not None and self._wait_in == "d1fwd") else None)
 
     def _forward_conv(self, B: int, training: bool, which: Optional[int] = None):
         lib, s = self.lib, self._s()
@@ -375,13 +387,18 @@ class MnistEngine:
             za, zb = g.data_ptr(), g.data_ptr() + 4 * first_conv
         xin = self.x_bufs[which or 0]
         if "conv1_fwd" not in self._SKIP:
-            self._chk(lib.hvd_conv1_fwd(xin.data_ptr(), self._p("c1", "kernel").data_ptr(),
-                                        self._p("c1", "bias").data_ptr(), self.a1.data_ptr(), B, za, na, zb, nb,
-                                        self.state.data_ptr(), int(which is not None), s), "conv1_fwd")
+            self._chk(lib.hvd_conv1_fwd_ex(xin.data_ptr(), self._p("c1", "kernel").data_ptr(),
+                                           self._p("c1", "bias").data_ptr(), self.a1.data_ptr(), B, za, na, zb, nb,
+                                           self.state.data_ptr(), int(which is not None), s,
+                                           self._conv1_bps if which is not None else 8), "conv1_fwd")
         if "fprop" not in self._SKIP:
-            self._chk(lib.hvd_conv2_fprop(self.a1.data_ptr(), self._p("c2", "kernel").data_ptr(),
-                                          self._p("c2", "bias").data_ptr(), self.p2.data_ptr(), self.mask2.data_ptr(),
-                                          self.state.data_ptr(), B, int(training), self.keep1, 0, s), "conv2_fprop")
+            # pipelined mode: CTA 0's spare warp also waits for the peers' rows of dense_1/kernel, so the Dense
+            # forward behind this kernel starts with the weights already delivered (HVD_WAIT_IN=d1fwd moves it back)
+            w = self.pipe.param_wait() if (self.pipe is not None and self._wait_in == "fprop") else None
+            self._chk(lib.hvd_conv2_fprop_ex(self.a1.data_ptr(), self._p("c2", "kernel").data_ptr(),
+                                             self._p("c2", "bias").data_ptr(), self.p2.data_ptr(), self.mask2.data_ptr(),
+                                             self.state.data_ptr(), B, int(training), self.keep1, 0, s,
+                                             ctypes.addressof(w) if w is not None else None), "conv2_fprop")
 
     def _head(self, B: int, training: bool, backward: bool, which: int = 0, probs: bool = False):
         gp = (lambda k, sh: self._g(k, sh, which).data_ptr()) if backward else (lambda k, sh: None)
@@ -442,7 +459,8 @@ class MnistEngine:
         lib, fused = self.lib, self.fused
         main = torch.cuda.current_stream(self.dev)
         s = self._s()
-        if self._fused_bwd and not ({"dgrad", "wgrad"} & self._SKIP):
+        fused_one = self._fused_bwd and not ({"dgrad", "wgrad"} & self._SKIP)
+        if fused_one:
             # ONE kernel: every CTA does its share of conv2 wgrad strips, then its share of dgrad tiles (with
             # conv1's ReLU backward and weight/bias gradient fused in); CTA 0 also publishes the step's
             # loss/accuracy into the pinned host ring.  dense1's dW (side2) only has to be done before the update.
@@ -468,11 +486,14 @@ class MnistEngine:
                                               None, B, self._dgrad_ctas, s, self.x_bufs[which].data_ptr(),
                                               self._g("c1", "kernel", which).data_ptr(),
                                               self._g("c1", "bias", which).data_ptr()), "conv2_dgrad")
-        main.wait_stream(self.side2)
+        if not (fused_one and self.pipe is not None):
+            main.wait_stream(self.side2)         # (pipelined + one-kernel conv backward: nothing was forked onto side2)
         if self.pipe is not None:
             main.wait_stream(self.side)          # dense1 dW (pushed to its owners) joins here
             if "b1" not in self._SKIP:
                 self.pipe.launch_tail(which, which, self.m.optimizer.hyper_row(which).data_ptr())
+                if self._ag_where == "tail":     # A/B switch: deliver the rows right behind the tail (exposed)
+                    self.pipe.launch_allgather()
         elif fused is not None and "b1" not in self._SKIP:
             for i in range(1 if self._bucket_mode == "overlap" else 0, len(fused.buckets)):
                 fused.run_bucket(i, which, self._exit_barrier(), hyper_row=which)
@@ -485,8 +506,20 @@ class MnistEngine:
         anything outside the training step reads parameters or optimizer state)."""
         torch.cuda.current_stream(self.dev).wait_stream(self.side)
         if self.pipe is not None:
-            # ... and for the weights that OTHER GPUs' tail kernels are still storing into this arena
+            self.flush_params()
+            # ... and wait for the rows that the OTHER ranks deliver into this arena (their next training step,
+            # their own sync or their end-of-epoch flush sends them)
             self.pipe.launch_param_wait()
+
+    def flush_params(self):
+        """Pipelined mode: deliver the rows of dense_1/kernel this rank owns to the other replicas if a training
+        step has updated them since the last delivery (normally the NEXT step does it, hidden under its conv
+        forward).  Non-blocking, one small launch; ``fit`` calls it at every epoch end and the blocking
+        ``train_on_batch`` after every step, so that a rank reading weights never waits on a peer that has
+        simply stopped training."""
+        if self.pipe is not None and self._ag_pending:
+            self.pipe.launch_allgather()
+            self._ag_pending = False
 
     def _stage_host(self, x, y):
         """Enqueue the H2D copy of one host batch into the input buffers of the NEXT step's parity on the
@@ -555,7 +588,9 @@ class MnistEngine:
 
     def train_host_batch(self, x, y):
         """Blocking end-to-end step from HOST arrays; returns (loss, accuracy) as Python floats."""
-        return self.train_host_batch_async(x, y).result()
+        out = self.train_host_batch_async(x, y).result()
+        self.flush_params()
+        return out
 
     def train_step(self, x: torch.Tensor, y: torch.Tensor):
         B = x.shape[0]
@@ -602,6 +637,7 @@ class MnistEngine:
                     raise RuntimeError("unfused optimizer path expects a single gradient buffer")
                 opt.apply_gradients(self.m.arena)
         self._ev_done[which].record(main)
+        self._ag_pending = True
         if fused is not None:
             opt.iterations += 1
             self._parity ^= 1 if self.m.arena.n_grad_bufs == 2 else 0
@@ -616,6 +652,12 @@ class MnistEngine:
         stream, C, join."""
         main = torch.cuda.current_stream(self.dev)
         fused = self.fused
+        if self.pipe is not None and self.pipe.n > 1 and self._ag_where == "start":
+            # the rows of dense_1/kernel this rank updated in the previous step travel to the other replicas NOW,
+            # from a few small CTAs that share the SMs with the conv forward; dense1's forward waits on their flags
+            self._ev_b.record(main)
+            self.side.wait_event(self._ev_b)
+            self.pipe.launch_allgather(stream=self.side)
         self._part_a(B, which)
         self._part_b(B, which)
         forked = False

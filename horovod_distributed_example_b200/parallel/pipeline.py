@@ -35,8 +35,15 @@ class HvdRsPush(ctypes.Structure):
 
 
 class HvdParamWait(ctypes.Structure):
-    _fields_ = [("counter", ctypes.c_void_p), ("target", ctypes.c_void_p), ("error", ctypes.c_void_p),
-                ("timeout_ns", ctypes.c_ulonglong)]
+    _fields_ = [("flags", ctypes.c_void_p), ("version", ctypes.c_void_p), ("error", ctypes.c_void_p),
+                ("timeout_ns", ctypes.c_ulonglong), ("rank", ctypes.c_int), ("nranks", ctypes.c_int),
+                ("ag_ctas", ctypes.c_int), ("trace", ctypes.c_void_p)]
+
+
+class HvdAllgatherArgs(ctypes.Structure):
+    _fields_ = [("w0", ctypes.c_longlong), ("w1", ctypes.c_longlong), ("param_off", ctypes.c_longlong),
+                ("version", ctypes.c_void_p * MAX_RANKS), ("use_mc", ctypes.c_int),
+                ("trace", ctypes.c_void_p * MAX_RANKS)]
 
 
 class HvdTailArgs(ctypes.Structure):
@@ -45,7 +52,7 @@ class HvdTailArgs(ctypes.Structure):
                 ("grad_off", ctypes.c_longlong), ("param_off", ctypes.c_longlong),
                 ("slot0_off", ctypes.c_longlong), ("slot1_off", ctypes.c_longlong),
                 ("recv", ctypes.c_void_p * MAX_RANKS), ("ll", ctypes.c_void_p * MAX_RANKS),
-                ("ready_target", ctypes.c_void_p * MAX_RANKS), ("hyper", ctypes.c_void_p),
+                ("version", ctypes.c_void_p * MAX_RANKS), ("hyper", ctypes.c_void_p),
                 ("scale", ctypes.c_float), ("kind", ctypes.c_int), ("parity", ctypes.c_int),
                 ("ll_ctas", ctypes.c_int), ("use_mc", ctypes.c_int), ("trace", ctypes.c_void_p * MAX_RANKS)]
 
@@ -58,6 +65,9 @@ def _declare(lib):
     lib.hvd_tail_launch.argtypes = [P(HvdCommCtx), P(HvdTailArgs), ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
     lib.hvd_param_wait_launch.restype = ctypes.c_int
     lib.hvd_param_wait_launch.argtypes = [P(HvdParamWait), ctypes.c_void_p]
+    lib.hvd_allgather_launch.restype = ctypes.c_int
+    lib.hvd_allgather_launch.argtypes = [P(HvdCommCtx), P(HvdAllgatherArgs), ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                         ctypes.c_int]
     lib.hvd_rs_flags_launch.restype = ctypes.c_int
     lib.hvd_rs_flags_launch.argtypes = [P(HvdRsPush), ctypes.c_void_p]
     lib._hvd_pipe_declared = True
@@ -73,7 +83,8 @@ class PipelinedStep:
     slab that hold the small tensors (in front of and behind the big one), ``big`` is the big tensor's range."""
 
     def __init__(self, ctx: peer_mod.PeerContext, arena_buf: peer_mod.SymmBuffer, base_off: int, arena, kind: int,
-                 small_a, big, small_b, ll_ctas: Optional[int] = None, ctas: Optional[int] = None):
+                 small_a, big, small_b, ll_ctas: Optional[int] = None, ctas: Optional[int] = None,
+                 ag_ctas: Optional[int] = None):
         self.ctx, self.buf, self.base_off, self.arena, self.kind = ctx, arena_buf, base_off, arena, kind
         self.lib = native.cuda_lib()
         _declare(self.lib)
@@ -93,7 +104,11 @@ class PipelinedStep:
         self.rs = ctx.alloc(w * 4, multicast=False)                      # [src][shard] floats
         self.ll = ctx.alloc(2 * n * self.npk * 16, multicast=False)      # [parity][src][packet] x 16 B
         n_local = n if ctx.emulated else 1
-        self._targets = [torch.zeros(1, dtype=torch.int32, device=ctx.device) for _ in range(n_local)]
+        # number of updates applied to the big tensor (device word per local rank; written by the tail kernel)
+        self._versions = [torch.zeros(1, dtype=torch.int32, device=ctx.device) for _ in range(n_local)]
+        # all-gather CTAs: ~36 KB of rows each, at most 256 (rank, CTA) delivery flags for the readers to check
+        shard_bytes = self.shard * 4
+        self.ag_ctas = ag_ctas or max(8, min(32, 256 // max(n, 1), (shard_bytes + 16383) // 16384))
         # One CTA per SM: 256-thread CTAs, the LL part wants one packet per thread, the rest stream the shard
         self.ll_ctas = ll_ctas or max(1, min(64, (self.npk + 255) // 256))
         total = ctas or 296                # two 256-thread CTAs per SM: the shard part is a bandwidth-bound stream
@@ -103,9 +118,13 @@ class PipelinedStep:
         self.ctas = max(total, self.ll_ctas + 1)
         import os
         self.flag_kernel = os.environ.get("HVD_RS_FLAG_KERNEL", "1") != "0"
-        self.use_mc = bool(arena_buf.mc_ptr) and n > 1 and os.environ.get("HVD_TAIL_MC", "1") != "0"
+        self.ag_tma = os.environ.get("HVD_AG_TMA", "1") != "0"      # all-gather by TMA bulk copies (one warp per CTA)
+        # multimem.st sends each row once and lets the switch replicate it; with a single peer a plain peer store
+        # is the same traffic and measured faster
+        self.use_mc = bool(arena_buf.mc_ptr) and n > 1 and os.environ.get("HVD_AG_MC", "1" if n > 2 else "0") != "0"
         self._rs_cache = {}
         self._wait = None
+        self._ag_args = None
         # device-side trace ring (64 steps x 16 globaltimer stamps) - HVD_TIMELINE on the engine path, profiling
         self._trace = None
 
@@ -140,7 +159,7 @@ class PipelinedStep:
         if rc != 0:
             raise RuntimeError(f"hvd_rs_flags_launch failed: {rc}")
 
-    def counter_ptr(self, rank: Optional[int] = None) -> int:
+    def flags_ptr(self, rank: Optional[int] = None) -> int:
         r = (rank or 0) if self.ctx.emulated else self.ctx.rank
         return self.ctx.pad.ptrs[r] + 4 * ((SLOT_READY * MAX_CTAS) * MAX_RANKS)
 
@@ -150,10 +169,13 @@ class PipelinedStep:
             return None
         if self.ctx.emulated or self._wait is None:
             w = HvdParamWait()
-            w.counter = self.counter_ptr(rank)
-            w.target = self._targets[self._rank_index(rank)].data_ptr()
+            w.flags = self.flags_ptr(rank)
+            w.version = self._versions[self._rank_index(rank)].data_ptr()
             w.error = self.ctx._err.data_ptr()
             w.timeout_ns = self.ctx.timeout_ns
+            w.rank = (rank or 0) if self.ctx.emulated else self.ctx.rank
+            w.nranks, w.ag_ctas = self.n, self.ag_ctas
+            w.trace = self._trace[self._rank_index(rank)].data_ptr() if self._trace is not None else None
             if self.ctx.emulated:
                 return w
             self._wait = w
@@ -171,7 +193,7 @@ class PipelinedStep:
         for r in range(self.n):
             a.recv[r] = self.rs.ptrs[r]
             a.ll[r] = self.ll.ptrs[r]
-            a.ready_target[r] = self._targets[self._rank_index(r)].data_ptr()
+            a.version[r] = self._versions[self._rank_index(r)].data_ptr()
             a.trace[r] = self._trace[self._rank_index(r)].data_ptr() if self._trace is not None else None
         a.hyper = hyper_ptr
         a.scale = 1.0 / self.n
@@ -181,6 +203,7 @@ class PipelinedStep:
     def enable_trace(self) -> None:
         """Must be called before the step is captured into a CUDA graph (the pointer is a kernel argument)."""
         if self._trace is None:
+            self._wait = self._ag_args = None          # cached structs carry the trace pointer
             n_local = self.n if self.ctx.emulated else 1
             self._trace = [torch.zeros(64, 16, dtype=torch.int64, device=self.ctx.device) for _ in range(n_local)]
 
@@ -198,9 +221,30 @@ class PipelinedStep:
             msg = self.lib.hvd_cuda_error_string(rc).decode() if rc > 0 else f"bad arguments ({rc})"
             raise RuntimeError(f"hvd_tail_launch failed: {msg}")
 
-    def launch_param_wait(self, stream=None) -> None:
-        """Make ``stream`` wait until every weight the peers' last tail kernels sent has landed in this arena."""
-        w = self.param_wait()
+    def launch_allgather(self, stream=None) -> None:
+        """Deliver this rank's rows of the big tensor (current version) to every other replica.  Idempotent;
+        enqueued at the start of every training step and by ``flush``.  No-op at size 1."""
+        if self.n == 1:
+            return
+        a = self._ag_args
+        if a is None:
+            a = self._ag_args = HvdAllgatherArgs()
+            a.w0, a.w1 = self.big
+            a.param_off = self.base_off + self.arena.param_offset
+            for r in range(self.n):
+                a.version[r] = self._versions[self._rank_index(r)].data_ptr()
+                a.trace[r] = self._trace[self._rank_index(r)].data_ptr() if self._trace is not None else None
+            a.use_mc = int(self.use_mc)
+        rc = self.lib.hvd_allgather_launch(ctypes.byref(self.ctx.comm_ctx(self.buf)), ctypes.byref(a), self.ag_ctas,
+                                           self.ctx._stream(stream), self.n if self.ctx.emulated else 0,
+                                           int(self.ag_tma))
+        if rc != 0:
+            msg = self.lib.hvd_cuda_error_string(rc).decode() if rc > 0 else f"bad arguments ({rc})"
+            raise RuntimeError(f"hvd_allgather_launch failed: {msg}")
+
+    def launch_param_wait(self, stream=None, rank: Optional[int] = None) -> None:
+        """Make ``stream`` wait until every peer has delivered the current version of its rows into this arena."""
+        w = self.param_wait(rank)
         if w is None:
             return
         rc = self.lib.hvd_param_wait_launch(ctypes.byref(w), self.ctx._stream(stream))
@@ -231,5 +275,6 @@ class PipelinedStep:
         sm = self.npk * 8
         st = "multimem.st" if self.use_mc else "peer stores"
         return [f"big[{self.big[0]}:{self.big[1]}] {w}B: dW GEMM epilogue pushes tiles to their owner (reduce-scatter), "
-                f"owner update, {st} to every replica, deferred ready-counter wait; shard ctas={self.ctas - self.ll_ctas}",
+                f"owner update in the tail (shard ctas={self.ctas - self.ll_ctas}), all-gather by {self.ag_ctas} small CTAs "
+                f"under the next step's conv forward ({st}), readers wait on version flags",
                 f"small {sm}B: LL one-shot (flagged 16B packets, no barrier), ll ctas={self.ll_ctas}"]

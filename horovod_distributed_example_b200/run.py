@@ -79,8 +79,13 @@ def launch(np_: int, command: List[str], extra_env=None, master_port: int = 0, t
     cmd = command
     if cmd[0].endswith(".py"):
         cmd = [sys.executable] + cmd
+    # Like torchrun (and unlike a bare Popen): every rank would otherwise start one OpenMP/MKL worker per core of the
+    # host, and N ranks' spinning pools then slow each other's launch loop (measured: 106 vs 86 us/step at 2 ranks).
+    omp = str(max(1, min(4, (os.cpu_count() or 1) // max(np_, 1))))
     for r in range(np_):
         env = dict(os.environ)
+        if np_ > 1:
+            env.setdefault("OMP_NUM_THREADS", omp)
         env.update(extra_env or {})
         env.update({"HVD_RANK": str(r), "HVD_SIZE": str(np_), "HVD_LOCAL_RANK": str(r),
                     "HVD_LOCAL_SIZE": str(np_), "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port)})
