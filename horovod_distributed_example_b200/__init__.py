@@ -73,6 +73,8 @@ def stop_timeline() -> None:
     from .basics import state
     st = state()
     if st.timeline is not None:
+        for hook in list(st.shutdown_hooks):        # engines drain their device-side records first
+            hook()
         st.timeline.close()
         st.timeline = None
 

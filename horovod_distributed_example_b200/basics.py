@@ -21,7 +21,7 @@ import datetime
 import logging
 import os
 import socket
-from dataclasses import dataclass
+from dataclasses import dataclass, field
 from typing import Optional
 
 from .config import Config
@@ -45,6 +45,7 @@ class _State:
     peer: Optional[object] = None        # parallel.peer.PeerContext (lazily created)
     timeline: Optional[object] = None
     step: int = 0
+    shutdown_hooks: list = field(default_factory=list)     # run first by shutdown() (e.g. the engine's timeline drain)
 
 
 _state = _State()
@@ -165,12 +166,22 @@ def shutdown() -> None:
     """Tear down peer memory, the timeline and (if we created it) the process group."""
     if not _state.initialized:
         return
+    for hook in list(_state.shutdown_hooks):
+        try:
+            hook()
+        except Exception as e:  # pragma: no cover - best effort at exit
+            log.warning("shutdown hook failed: %s: %s", type(e).__name__, e)
+    _state.shutdown_hooks.clear()
     try:
         if _state.peer is not None:
             _state.peer.close()
     except Exception as e:  # pragma: no cover - best effort at exit
         log.debug("peer close failed: %s", e)
     _state.peer = None
+    import sys as _sys
+    _peer_mod = _sys.modules.get(__package__ + ".parallel.peer")
+    if _peer_mod is not None:
+        _peer_mod.reset()                # a later init() builds a fresh context (fresh epochs, pads, buffers)
     if _state.timeline is not None:
         _state.timeline.close()
         _state.timeline = None

@@ -20,7 +20,7 @@ from typing import Iterable, Optional
 import torch
 
 from . import basics
-from .basics import _state, _require_init
+from .basics import _require_init, _state, log
 from .utils import nvtx
 
 # Horovod reduce-op constants (later Horovod versions; `average=` is the 0.18 spelling).
@@ -77,6 +77,19 @@ def _fault_skip() -> bool:
     cfg = _state.config
     f = cfg.parsed_fault() if cfg else None
     return bool(f and f[0] == _state.rank and f[1] == _state.step)
+
+
+def _fault_stall() -> None:
+    """HVD_FAULT_INJECT=rank:step fired on this rank: behave like a rank that hangs - stop participating (the
+    peers' in-kernel waits run into their bound and name this rank), then fail.  Skipping the step and carrying on
+    would not model a failure: the per-rank epoch counters would be off by one and the next step's packets would be
+    taken for this one's."""
+    import time
+    cfg = _state.config
+    wait = (cfg.barrier_abort_time() if cfg else 0.0) or 60.0
+    log.error("HVD_FAULT_INJECT: rank %d stalls at step %d", _state.rank, _state.step)
+    time.sleep(wait + 10.0)
+    raise RuntimeError(f"fault injected: rank {_state.rank} stalled at step {_state.step}")
 
 
 def allreduce_(tensor: torch.Tensor, average: bool = True, name: Optional[str] = None,

@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(256, 2) hvd_tail_kernel(HvdCommCtx c, HvdTailA
     if (tr_sh) tr[7] = globaltimer_ns();
     if (d == 0 && tid == 0) *a.version[rank] = ep;          // read by the all-gather / the readers' wait (stream order)
   }
-  if (tr_ll) tr[3] = globaltimer_ns();
+  if (tr_ll) { tr[3] = globaltimer_ns(); tr[15] = ep; }      // [15]: which step this record belongs to
   hvd_epoch_store(c, HVD_SLOT_TAIL, ep);
 }
 
@@ -448,6 +448,13 @@ extern "C" int hvd_tail_launch(const HvdCommCtx* c, const HvdTailArgs* a, int ct
     default: return -7;
   }
   return (int)e;
+}
+
+// One %globaltimer reading (ns) into *out - lets the host line device stamps up with its own clock.
+__global__ void hvd_globaltimer_kernel(unsigned long long* out) { *out = globaltimer_ns(); }
+extern "C" int hvd_globaltimer_probe(unsigned long long* out, void* stream) {
+  hvd_globaltimer_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(out);
+  return (int)cudaGetLastError();
 }
 
 extern "C" int hvd_param_wait_launch(const HvdParamWait* w, void* stream) {

@@ -30,7 +30,7 @@ from typing import Optional
 import torch
 
 from .. import basics
-from ..collectives import _fault_skip
+from ..collectives import _fault_skip, _fault_stall
 from ..keras import layers as L
 from ..keras import losses as losses_mod
 from ..ops import native
@@ -214,6 +214,7 @@ class MnistEngine:
         self._parity = 0
         self._ag_pending = False
         self._conv1_bps = 8
+        self._tl_offset, self._tl_done, self._tl_active = None, 0, False
         self._ag_where = os.environ.get("HVD_AG_WHERE", "start")
         self._wait_in = os.environ.get("HVD_WAIT_IN", "fprop")
         self.side = torch.cuda.Stream(device=dev)
@@ -274,6 +275,9 @@ class MnistEngine:
                 self._conv1_bps = int(os.environ.get("HVD_CONV1_BPS", 7))
             if os.environ.get("HVD_TAIL_TRACE", "0") == "1" or basics.state().timeline is not None:
                 self.pipe.enable_trace()
+            if basics.state().timeline is not None:
+                self._tl_active = True
+                basics.state().shutdown_hooks.append(lambda: self.drain_timeline(final=True))
         elif hasattr(opt, "_pipe"):
             opt._pipe = None
         cfg = basics.state().config
@@ -511,6 +515,41 @@ class MnistEngine:
             # their own sync or their end-of-epoch flush sends them)
             self.pipe.launch_param_wait()
 
+    # ------------------------------------------------------------------ HVD_TIMELINE on the engine path
+    _TL_EVENTS = ((0, 3, "grad.small_tensors", "FUSED_ALLREDUCE_UPDATE_LL"),
+                  (4, 7, "grad.dense_1/kernel", "FUSED_ALLREDUCE_UPDATE_OWNER_ROWS"),
+                  (10, 11, "param.dense_1/kernel", "ALLGATHER_UPDATED_ROWS"),
+                  (12, 13, "param.dense_1/kernel", "WAIT_PEER_ROWS"))
+
+    def drain_timeline(self, final: bool = False):
+        """Write the tail kernel's own device timestamps (pipeline_tail.cu: %globaltimer stamps in a page-locked
+        ring) into the Chrome trace as complete events, one set per training step.  Lazy and sync-free: only
+        records at least 12 steps behind the launches are read (``final`` synchronizes and takes the rest)."""
+        tl = basics.state().timeline
+        if tl is None or self.pipe is None or self.pipe._trace is None:
+            return
+        if self._tl_offset is None:
+            self._tl_offset = self.pipe.device_clock_offset_us(tl.now_us)
+        if final:
+            torch.cuda.synchronize(self.dev)
+        ring = self.pipe._trace_np[0]
+        upto = self._train_steps if final else self._train_steps - 12
+        while self._tl_done < upto:
+            step = self._tl_done + 1
+            if self._train_steps - step >= 60:         # overwritten by newer steps before it was read
+                self._tl_done += 1
+                continue
+            ep = (self.pipe.epoch0 + step) & 0xFFFFFFFF
+            row = ring[ep & 63]
+            if int(row[15]) != ep:
+                break
+            for a, b, tensor, name in self._TL_EVENTS:
+                t0, t1 = int(row[a]), int(row[b])
+                # the all-gather / wait stamps of the LAST step only exist once another step (or a flush) ran
+                if t0 > 0 and t1 >= t0 and (a < 8 or t0 >= int(row[0])):
+                    tl.complete(tensor, name, int(t0 / 1e3 + self._tl_offset), max(1, int((t1 - t0) / 1e3)))
+            self._tl_done += 1
+
     def flush_params(self):
         """Pipelined mode: deliver the rows of dense_1/kernel this rank owns to the other replicas if a training
         step has updated them since the last delivery (normally the NEXT step does it, hidden under its conv
@@ -614,8 +653,8 @@ class MnistEngine:
             opt.begin_step()
         if fused is not None:
             fused.ctx.check_error()          # host watchdog (reads one pinned word; no sync)
-            if self._fault is not None and _fault_skip():   # HVD_FAULT_INJECT=rank:step: this rank skips the step
-                return
+            if self._fault is not None and _fault_skip():   # HVD_FAULT_INJECT=rank:step: this rank hangs, then fails
+                _fault_stall()
         which = self._which()
         main = self._main()
         nvtx.push("hvd.step")
@@ -645,6 +684,8 @@ class MnistEngine:
                 self.sync_params()           # the replica checksum must see the weights peers are still sending
                 opt._debug_after_step(self.m.arena, which)
         self._train_steps += 1
+        if self._tl_active and (self._train_steps & 15) == 0:
+            self.drain_timeline()
         nvtx.pop()
 
     def _whole_step(self, B: int, which: int):

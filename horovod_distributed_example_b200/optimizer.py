@@ -143,8 +143,8 @@ class _DistributedMixin:
         if self._fused is not None and self._compression is Compression.none:
             # fused peer-memory path: reduce + scale + update in one kernel per bucket
             self._fused.ctx.check_error()      # host watchdog: a barrier that timed out names the stalled peer
-            if collectives._fault_skip():      # HVD_FAULT_INJECT=rank:step - this rank "dies" for one step
-                return
+            if collectives._fault_skip():      # HVD_FAULT_INJECT=rank:step - this rank hangs, then fails
+                collectives._fault_stall()
             self.iterations += 1
             if self._hooked:
                 for bi in range(len(self._buckets)):      # anything the hooks did not launch (unused params)

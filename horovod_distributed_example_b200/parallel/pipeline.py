@@ -125,6 +125,10 @@ class PipelinedStep:
         self._rs_cache = {}
         self._wait = None
         self._ag_args = None
+        # the tail kernel numbers its steps with the context's epoch counter, which may already have advanced
+        # (another model trained on this context before): step k of THIS object carries epoch epoch0 + k
+        torch.cuda.synchronize(ctx.device)
+        self.epoch0 = int(ctx._epochs[0][SLOT_TAIL * MAX_CTAS].item()) & 0xFFFFFFFF
         # device-side trace ring (64 steps x 16 globaltimer stamps) - HVD_TIMELINE on the engine path, profiling
         self._trace = None
 
@@ -201,16 +205,33 @@ class PipelinedStep:
         return a
 
     def enable_trace(self) -> None:
-        """Must be called before the step is captured into a CUDA graph (the pointer is a kernel argument)."""
+        """Must be called before the step is captured into a CUDA graph (the pointer is a kernel argument).
+        The ring lives in page-locked host memory that the kernels write directly (a handful of 8-byte stores per
+        step), so the host can read finished records without touching the stream."""
         if self._trace is None:
             self._wait = self._ag_args = None          # cached structs carry the trace pointer
             n_local = self.n if self.ctx.emulated else 1
-            self._trace = [torch.zeros(64, 16, dtype=torch.int64, device=self.ctx.device) for _ in range(n_local)]
+            self._trace = [torch.zeros(64, 16, dtype=torch.int64).pin_memory() for _ in range(n_local)]
+            self._trace_np = [t.numpy() for t in self._trace]
 
     def read_trace(self, rank: int = 0) -> torch.Tensor:
         """[64][16] int64 nanosecond stamps (rows indexed by step epoch & 63); synchronizes the device."""
         torch.cuda.synchronize(self.ctx.device)
-        return self._trace[self._rank_index(rank)].cpu()
+        return self._trace[self._rank_index(rank)].clone()
+
+    def device_clock_offset_us(self, now_us=None) -> float:
+        """``now_us()`` (default: the monotonic clock in us) minus the device %globaltimer in us, from one probe
+        kernel (error: a launch + sync, ~10 us)."""
+        import time
+        now_us = now_us or (lambda: time.monotonic() * 1e6)
+        probe = torch.zeros(1, dtype=torch.int64).pin_memory()
+        self.lib.hvd_globaltimer_probe.restype = ctypes.c_int
+        self.lib.hvd_globaltimer_probe.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        rc = self.lib.hvd_globaltimer_probe(probe.data_ptr(), self.ctx._stream(None))
+        if rc != 0:
+            raise RuntimeError(f"hvd_globaltimer_probe failed: {rc}")
+        torch.cuda.synchronize(self.ctx.device)
+        return now_us() - float(probe[0]) / 1e3
 
     # ------------------------------------------------------------------ launches
     def launch_tail(self, grad_buf: int, parity: int, hyper_ptr: int, stream=None) -> None:

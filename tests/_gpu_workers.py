@@ -26,11 +26,57 @@ def collectives():
             out = hvd.allreduce(t, average=True)
             torch.testing.assert_close(out, exp, rtol=1e-6, atol=1e-6)
     hvd.basics.state().config.allreduce_variant = "auto"
+    _fused_update_variants(ctx, r, n)
     b = hvd.broadcast(torch.arange(1000.0, device="cuda") * (r + 1), root_rank=n - 1)
     assert torch.equal(b, torch.arange(1000.0, device="cuda") * n)
     torch.cuda.synchronize()
     ctx.check_error()
     print("OK", flush=True)
+
+
+def _fused_update_variants(ctx, r, n):
+    """allreduce + 1/N + Adadelta/Adam in ONE kernel on real ranks, every variant the box offers (NVLS included:
+    multimem cannot be emulated on one GPU) against a CPU oracle on the mean gradient; replicas bit-identical."""
+    from horovod_distributed_example_b200.keras import optimizers as O
+    from horovod_distributed_example_b200.parallel import buckets as B
+    from horovod_distributed_example_b200.parallel.arena import ParamArena
+    from horovod_distributed_example_b200.parallel.fused import FusedReducer
+    from horovod_distributed_example_b200.parallel.peer import NVLS, ONESHOT, TWOSHOT, VARIANT_NAMES
+    specs = [("d2/b", (10,)), ("d2/k", (128, 10)), ("d1/b", (128,)), ("d1/k", (600, 128)), ("c/k", (3, 3, 4, 8))]
+    variants = [ONESHOT, TWOSHOT] + ([NVLS] if ctx.multicast else [])
+    for variant in variants:
+        for mk in (lambda: O.Adadelta(2.0), lambda: O.Adam(0.01)):
+            opt = mk()
+            arena = ParamArena(specs, "cuda", n_slots=opt.n_slots, allocator=ctx.alloc_tensor)
+            opt.bind(arena)
+            buckets = B.plan(arena, 64 << 20, ["d1/k"])
+            red = FusedReducer(arena, opt, buckets, ctx, variants=[variant] * len(buckets))
+            cpu_opt = mk()
+            cpu = ParamArena(specs, "cpu", n_slots=opt.n_slots)
+            cpu_opt.bind(cpu)
+            g = torch.Generator().manual_seed(5)
+            p0 = torch.randn(arena.n, generator=g)
+            cpu.params.copy_(p0)
+            arena.params.copy_(p0)
+            for step in range(3):
+                grads = torch.randn(n, arena.n, generator=g)          # every rank draws every rank's gradients
+                arena.grads.copy_(grads[r])
+                torch.cuda.synchronize()
+                hvd.barrier()
+                red.run_all()
+                opt.iterations += 1
+                opt._push_hyper()
+                torch.cuda.synchronize()
+                ctx.check_error()
+                mean = grads[0].clone()
+                for k in range(1, n):
+                    mean += grads[k]
+                cpu.grads.copy_(mean * (1.0 / n))
+                cpu_opt.apply_gradients(cpu)
+                torch.testing.assert_close(arena.params.cpu(), cpu.params, rtol=3e-5, atol=3e-6)
+            cs = hvd.allgather_object(int(arena.checksum()))
+            assert all(c == cs[0] for c in cs), (VARIANT_NAMES[variant], cs)
+    print(f"rank {r}: fused update variants {[VARIANT_NAMES[v] for v in variants]} match the oracle", flush=True)
 
 
 def train_replicas():
@@ -125,6 +171,33 @@ def torchmodel_overlap():
     torch.testing.assert_close(got, exp, rtol=1e-3, atol=1e-5)
     hvd.barrier()
     print("OK", flush=True)
+
+
+def fault_inject():
+    """HVD_FAULT_INJECT=1:3 (set by the test): rank 1 stops participating at step 3.  Every other rank's tail kernel
+    runs into its bounded wait, raises the error word, and the host names the missing rank; the process exits
+    non-zero and hvdrun tears the whole group down (the stalled rank included)."""
+    hvd.init()
+    r = hvd.rank()
+    m = keras.Sequential([
+        keras.layers.Conv2D(32, (3, 3), activation='relu', input_shape=(28, 28, 1)),
+        keras.layers.Conv2D(64, (3, 3), activation='relu'),
+        keras.layers.MaxPooling2D((2, 2)), keras.layers.Dropout(0.25), keras.layers.Flatten(),
+        keras.layers.Dense(128, activation='relu'), keras.layers.Dropout(0.5),
+        keras.layers.Dense(10, activation='softmax')], seed=1)
+    m.compile(loss=keras.losses.SparseCategoricalCrossentropy(),
+              optimizer=hvd.DistributedOptimizer(keras.optimizers.Adadelta(1.0)), metrics=['accuracy'])
+    rng = np.random.default_rng(r)
+    x = rng.random((128, 28, 28, 1), dtype=np.float32)
+    y = rng.integers(0, 10, 128)
+    try:
+        for step in range(6):
+            m.train_on_batch(x, y)
+            print(f"rank {r}: step {step + 1} done", flush=True)
+    except RuntimeError as e:
+        print(f"FAULT-DETECTED rank {r}: {e}", flush=True)
+        os._exit(3)              # a failed rank does not run the collective teardown
+    print(f"rank {r}: UNEXPECTED - all steps finished", flush=True)
 
 
 if __name__ == "__main__":

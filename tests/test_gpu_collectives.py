@@ -157,9 +157,10 @@ def test_barrier_timeout_sets_error_word():
         ctx.check_error()
 
 
-def _run_multi(nproc, body, timeout=300):
+def _run_multi(nproc, body, timeout=300, extra_env=None):
     env = dict(os.environ)
     env["HVD_TEST_BODY"] = body
+    env.update(extra_env or {})
     return subprocess.run([sys.executable, "-m", "horovod_distributed_example_b200.run", "-np", str(nproc),
                            "--timeout", str(timeout), os.path.join(ROOT, "tests", "_gpu_workers.py")],
                           cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout + 60)
@@ -175,3 +176,26 @@ def test_multi_gpu(body):
     r = _run_multi(min(n, 8), body)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("OK") >= min(n, 8)
+
+
+@pytest.mark.multigpu
+def test_fault_injection_on_real_ranks():
+    """SURVEY section 5.3 end to end: rank 1 hangs at step 3 (HVD_FAULT_INJECT=1:3).  The other ranks' in-kernel
+    waits give up after the shutdown time, the host error names rank 1, and hvdrun kills the group."""
+    _need_gpu()
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import time
+    t0 = time.time()
+    r = _run_multi(min(n, 8), "fault_inject", timeout=120,
+                   extra_env={"HVD_FAULT_INJECT": "1:3", "HVD_STALL_CHECK_TIME_SECONDS": "1",
+                              "HVD_STALL_SHUTDOWN_TIME_SECONDS": "3"})
+    out = r.stdout + r.stderr
+    assert r.returncode != 0, out[-3000:]
+    # (a step's loss is published before its tail kernel runs, so step 3 itself may still report; step 4 cannot)
+    assert "rank 0: step 2 done" in out and "rank 0: step 4 done" not in out, out[-3000:]
+    assert "FAULT-DETECTED rank 0" in out and "waited for rank 1" in out, out[-3000:]
+    assert "terminating the job" in out, out[-3000:]
+    assert "UNEXPECTED" not in out
+    assert time.time() - t0 < 100

@@ -296,6 +296,36 @@ def test_engine_matches_torch_oracle_without_dropout(opt_name, env, monkeypatch)
     hvd.shutdown()
 
 
+def test_engine_timeline_has_one_update_event_per_step(tmp_path, monkeypatch):
+    """HVD_TIMELINE on the path users run (the graph-captured engine): the tail kernel stamps %globaltimer into a
+    page-locked ring and the engine drains it lazily - a 10-step run leaves 10 FUSED_ALLREDUCE_UPDATE_LL and 10
+    FUSED_ALLREDUCE_UPDATE_OWNER_ROWS complete events with plausible device durations."""
+    import json
+    _lib()
+    path = tmp_path / "timeline.json"
+    monkeypatch.setenv("HVD_TIMELINE", str(path))
+    import horovod_distributed_example_b200 as _hvd
+    _hvd.shutdown()                       # an earlier test may have left a world without a timeline behind
+    hvd, build = _models(0.25, 0.5, "adadelta")
+    m = build()
+    rng = np.random.default_rng(2)
+    x = rng.random((B, 28, 28, 1), dtype=np.float32)
+    y = rng.integers(0, 10, B)
+    for _ in range(10):
+        m.train_on_batch(x, y)
+    assert type(m._backend).__name__ == "MnistEngine" and m._backend.pipe is not None
+    assert hvd.basics.state().timeline is not None and m._backend._tl_active
+    m._backend.drain_timeline(final=True)          # (shutdown() does this too; called here so an error surfaces)
+    hvd.shutdown()
+    ev = [e for e in json.loads(path.read_text()) if isinstance(e, dict)]
+    ll = [e for e in ev if e.get("name") == "FUSED_ALLREDUCE_UPDATE_LL" and e.get("ph") == "X"]
+    own = [e for e in ev if e.get("name") == "FUSED_ALLREDUCE_UPDATE_OWNER_ROWS" and e.get("ph") == "X"]
+    assert len(ll) == 10 and len(own) == 10, (len(ll), len(own))
+    assert all(0 < e["dur"] < 1000 for e in ll + own)                  # microseconds of device time
+    ts = [e["ts"] for e in ll]
+    assert ts == sorted(ts)
+
+
 def test_engine_trains_with_dropout_and_partial_batch(monkeypatch):
     _lib()
     monkeypatch.setenv("HVD_DEBUG_GUARD", "1")      # red zones around every activation buffer
