@@ -104,6 +104,11 @@ def main():
                     best = (t, ctas)
             row[name + "_us"], row[name + "_ctas"] = best
             row[name + "_busbw_GBs"] = size / best[0] * 1e-3 * 2 * (n - 1) / n
+        if size <= P.LL_MAX_BYTES:
+            ll_fn = lambda: ctx.launch_ll(buf, 0, max_bytes // 4, nel, 1.0 / n)
+            row["ll_us"] = time_graph(ll_fn)
+            row["ll_ctas"] = (nel // 2 + 255) // 256
+            row["ll_busbw_GBs"] = size / row["ll_us"] * 1e-3 * 2 * (n - 1) / n
         nccl_fn = lambda: dist.all_reduce(nccl_t[:nel])
         t = time_graph(nccl_fn) if size <= (4 << 20) else time_fn(nccl_fn, iters)
         row["nccl_us"] = t
@@ -117,7 +122,7 @@ def main():
         # crossover table: largest size where one-shot is still the fastest of ours; smallest where NVLS wins
         one_max, nvls_min, cta_tab = 0, None, []
         for row in rows:
-            ours = {k: row[k + "_us"] for k in ("oneshot", "twoshot", "nvls") if k + "_us" in row}
+            ours = {k: row[k + "_us"] for k in ("oneshot", "twoshot", "nvls") if k + "_us" in row}   # (LL is picked by size)
             best = min(ours, key=ours.get)
             if best == "oneshot":
                 one_max = row["bytes"]

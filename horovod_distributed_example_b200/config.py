@@ -50,7 +50,7 @@ def _env_bool(name: str, default: bool = False) -> bool:
     return v.strip().lower() not in ("0", "false", "no", "off", "")
 
 
-ALLREDUCE_VARIANTS = ("auto", "oneshot", "twoshot", "nvls", "nccl")
+ALLREDUCE_VARIANTS = ("auto", "ll", "oneshot", "twoshot", "nvls", "nccl")
 
 
 @dataclass

@@ -95,6 +95,7 @@ class Optimizer:
         self._pin_ring = [torch.zeros(8, dtype=torch.float32).pin_memory() for _ in range(16)] \
             if arena.device.type == "cuda" else None
         self._pin_ev = [None] * 16
+        self._pin_np = None
         self._pin_i = 0
         self._push_hyper(both=True)
 
@@ -136,6 +137,27 @@ class Optimizer:
         else:
             for r in rows:
                 self._hyper[r].copy_(vals)
+
+    def _push_hyper_raw(self, row: int, memcpy_async, stream) -> None:
+        """Engine fast path: write this step's hyper-parameters into ``row`` with ONE 32-byte asynchronous copy on
+        ``stream`` (the engine's input-staging copy stream, next to the batch's own H2D copies), so that a
+        learning rate that changes every batch (warmup callback, Adam's lr_t) puts nothing on the compute stream.
+        ``memcpy_async(dst, src, nbytes, raw_stream)`` is the C ABI's cudaMemcpyAsync wrapper."""
+        k = self._pin_i % len(self._pin_ring)
+        self._pin_i += 1
+        ev = self._pin_ev[k]
+        if ev is not None:
+            ev.synchronize()
+        buf = self._pin_ring[k]
+        if self._pin_np is None:
+            self._pin_np = [b.numpy() for b in self._pin_ring]
+        self._pin_np[k][:] = self._hyper_values()
+        rc = memcpy_async(self._hyper[row & 1].data_ptr(), buf.data_ptr(), 32, stream.cuda_stream)
+        if rc:
+            raise RuntimeError(f"hyper-parameter copy failed with CUDA error {rc}")
+        if ev is None:
+            ev = self._pin_ev[k] = torch.cuda.Event()
+        ev.record(stream)
 
     @property
     def hyper(self) -> torch.Tensor:

@@ -215,6 +215,7 @@ class MnistEngine:
         self._ag_pending = False
         self._conv1_bps = 8
         self._tl_offset, self._tl_done, self._tl_active = None, 0, False
+        self._hyper_pushed = False
         self._ag_where = os.environ.get("HVD_AG_WHERE", "start")
         self._wait_in = os.environ.get("HVD_WAIT_IN", "fprop")
         self.side = torch.cuda.Stream(device=dev)
@@ -593,6 +594,13 @@ class MnistEngine:
         rc = lib.hvd_memcpy_async(self._x_ptr[w], xp, B * 3136, csh) or lib.hvd_memcpy_async(self._y_ptr[w], yp, B * 8, csh)
         if rc:
             raise RuntimeError(f"input staging copy failed with CUDA error {rc}")
+        opt = self.m.optimizer
+        if self.fused is not None and (opt._hyper_dirty > 0 or opt.kind == 3 or getattr(opt, "decay", 0.0) > 0.0):
+            # this step's row of the hyper-parameter block travels with the batch on the copy stream (the row's
+            # last readers were step t-2's update kernels, which _ev_done[w] above has already covered)
+            opt._push_hyper_raw(w, lib.hvd_memcpy_async, cs)
+            opt._hyper_dirty = max(0, opt._hyper_dirty - 1)
+            self._hyper_pushed = True
         self._ev_in[w].record(cs)
         main.wait_event(self._ev_in[w])
         return B
@@ -658,7 +666,9 @@ class MnistEngine:
         which = self._which()
         main = self._main()
         nvtx.push("hvd.step")
-        if fused is not None and (opt._hyper_dirty > 0 or opt.kind == 3 or getattr(opt, "decay", 0.0) > 0.0):
+        if self._hyper_pushed:
+            self._hyper_pushed = False           # _stage_host already sent this step's row on the copy stream
+        elif fused is not None and (opt._hyper_dirty > 0 or opt.kind == 3 or getattr(opt, "decay", 0.0) > 0.0):
             # this step's row of the hyper-parameter block (LR changed by a callback, Adam's lr_t, LR decay);
             # nothing in flight reads this row: its last readers were step t-2's update kernels
             opt._next_slot = which

@@ -60,8 +60,15 @@ class HvdFusedArgs(ctypes.Structure):
                 ("slot", ctypes.c_int), ("exit_barrier", ctypes.c_int)]
 
 
-ONESHOT, TWOSHOT, NVLS = 0, 1, 2
-VARIANT_NAMES = {ONESHOT: "oneshot", TWOSHOT: "twoshot", NVLS: "nvls"}
+class HvdLLArgs(ctypes.Structure):
+    _fields_ = [("in_off", ctypes.c_longlong), ("out_off", ctypes.c_longlong), ("n", ctypes.c_longlong),
+                ("scale", ctypes.c_float), ("ll", ctypes.c_void_p * MAX_RANKS), ("cap", ctypes.c_longlong)]
+
+
+ONESHOT, TWOSHOT, NVLS, LL = 0, 1, 2, 3
+VARIANT_NAMES = {ONESHOT: "oneshot", TWOSHOT: "twoshot", NVLS: "nvls", LL: "ll"}
+#: messages up to this size take the barrier-free LL one-shot kernel (packets of 2 floats + 2 flags)
+LL_MAX_BYTES = int(os.environ.get("HVD_LL_MAX_BYTES", 128 << 10))
 
 
 class _DevPtr:
@@ -101,6 +108,8 @@ def _declare(lib):
     lib.hvd_fused_allreduce_launch.restype = ctypes.c_int
     lib.hvd_fused_allreduce_launch.argtypes = [P(HvdCommCtx), P(HvdFusedArgs), ctypes.c_int, ctypes.c_int,
                                                ctypes.c_void_p, ctypes.c_int]
+    lib.hvd_ll_allreduce_launch.restype = ctypes.c_int
+    lib.hvd_ll_allreduce_launch.argtypes = [P(HvdCommCtx), P(HvdLLArgs), ctypes.c_void_p, ctypes.c_int]
     lib.hvd_bcast_launch.restype = ctypes.c_int
     lib.hvd_bcast_launch.argtypes = [P(HvdCommCtx), ctypes.c_int, ctypes.c_int, ctypes.c_longlong,
                                      ctypes.c_longlong, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
@@ -204,6 +213,7 @@ class PeerContext:
         self.staging_bytes = int(os.environ.get("HVD_STAGING_BYTES", 8 << 20))
         self.staging = self.alloc(self.staging_bytes)
         self._ctx_cache = {}
+        self._ll = None                      # receive buffers of the LL one-shot kernel (allocated on first use)
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -420,6 +430,22 @@ class PeerContext:
             msg = self.lib.hvd_cuda_error_string(rc).decode() if rc > 0 else f"bad arguments ({rc})"
             raise RuntimeError(f"hvd_fused_allreduce_launch failed: {msg}")
 
+    def launch_ll(self, buf: SymmBuffer, in_off: int, out_off: int, n: int, scale: float, stream=None):
+        """Barrier-free LL one-shot allreduce of ``n`` (even) floats at ``in_off`` of ``buf`` into ``out_off``.
+        Collective; the first call allocates the symmetric receive buffers (collective too)."""
+        cap = (LL_MAX_BYTES // 4 + 1) // 2
+        if self._ll is None:
+            self._ll = self.alloc(2 * self.size * cap * 16, multicast=False)
+        a = HvdLLArgs()
+        a.in_off, a.out_off, a.n, a.scale, a.cap = in_off, out_off, n, scale, cap
+        for r in range(self.size):
+            a.ll[r] = self._ll.ptrs[r]
+        rc = self.lib.hvd_ll_allreduce_launch(ctypes.byref(self.comm_ctx(buf)), ctypes.byref(a), self._stream(stream),
+                                              self.size if self.emulated else 0)
+        if rc != 0:
+            msg = self.lib.hvd_cuda_error_string(rc).decode() if rc > 0 else f"bad arguments ({rc})"
+            raise RuntimeError(f"hvd_ll_allreduce_launch failed: {msg}")
+
     def launch_bcast(self, buf: SymmBuffer, root: int, off: int, n: int, slot: int = SLOT_BCAST,
                      ctas: int = 0, stream=None):
         ctas = ctas or max(1, min(32, (n * 4 + 65535) // 65536))
@@ -502,6 +528,13 @@ class PeerContext:
     def _allreduce_range(self, buf: SymmBuffer, off: int, n: int, average: bool, stream=None,
                          out_off: Optional[int] = None):
         variant, ctas = self._pick(n * 4)
+        cfg = basics.state().config
+        forced = cfg.allreduce_variant if cfg else "auto"
+        if self.size > 1 and n * 4 <= LL_MAX_BYTES and n % 2 == 0 and off % 2 == 0 and \
+                (forced == "ll" or (forced == "auto" and variant == ONESHOT)):
+            self.launch_ll(buf, off, off if out_off is None else out_off, n, 1.0 / self.size if average else 1.0,
+                           stream=stream)
+            return
         if variant == NVLS and not buf.mc_ptr:
             variant = TWOSHOT
         if out_off is None and variant == ONESHOT:

@@ -60,6 +60,8 @@ def default_ctas(nbytes: int, variant: int, nranks: int) -> int:
 def pick(nbytes: int, nranks: int, has_nvls: bool, forced: str = "auto", forced_ctas: int = 0
          ) -> Tuple[int, int]:
     """Return (variant, ctas) for a message of ``nbytes`` across ``nranks``."""
+    if forced == "ll":
+        forced = "auto"          # LL applies to small tensor-level collectives only (peer.py); buckets pick as usual
     if forced in _NAMES:
         v = _NAMES[forced]
         if v == NVLS and not has_nvls:

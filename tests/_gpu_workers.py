@@ -18,7 +18,7 @@ def collectives():
     from horovod_distributed_example_b200.parallel import peer
     ctx = peer.context()
     print(f"rank {r}: backend={ctx.backend} multicast={ctx.multicast}", flush=True)
-    for forced in ("oneshot", "twoshot", "nvls"):
+    for forced in ("ll", "oneshot", "twoshot", "nvls", "auto"):
         hvd.basics.state().config.allreduce_variant = forced
         for numel in (1, 7, 1000, 300000, 3 << 20):
             t = torch.full((numel,), float(r + 1), device="cuda") + torch.arange(numel, device="cuda") % 5

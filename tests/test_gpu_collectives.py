@@ -67,6 +67,31 @@ def test_emulated_allreduce_matches_sum(ctx4, variant, n):
     torch.testing.assert_close(outs[0], ref, rtol=1e-6, atol=1e-6)
 
 
+@pytest.mark.parametrize("n", [2, 1000, 32768])
+def test_emulated_ll_allreduce_matches_sum(ctx4, n):
+    """The barrier-free LL one-shot kernel (small messages): in place and out of place, repeated launches (epoch
+    parity double-buffering), bit-identical on every rank."""
+    ctx = ctx4
+    buf = ctx.staging
+    torch.manual_seed(n)
+    vals = torch.randn(ctx.size, n, device="cuda")
+    ref = vals[0].clone()
+    for r in range(1, ctx.size):
+        ref += vals[r]
+    ref *= 1.0 / ctx.size
+    for rep in range(5):
+        out_off = 0 if rep % 2 else (1 << 18)
+        for r in range(ctx.size):
+            buf.peer_tensor(r)[:n].copy_(vals[r])
+        ctx.launch_ll(buf, 0, out_off, n, 1.0 / ctx.size)
+        torch.cuda.synchronize()
+        ctx.check_error()
+        outs = [buf.peer_tensor(r)[out_off:out_off + n].clone() for r in range(ctx.size)]
+        for o in outs:
+            assert torch.equal(o, outs[0])
+        torch.testing.assert_close(outs[0], ref, rtol=1e-6, atol=1e-6)
+
+
 def test_emulated_broadcast(ctx4):
     ctx = ctx4
     buf = ctx.staging
