@@ -192,7 +192,7 @@ def _run_multi(nproc, body, timeout=300, extra_env=None):
 
 
 @pytest.mark.multigpu
-@pytest.mark.parametrize("body", ["collectives", "train_replicas", "torchmodel_overlap"])
+@pytest.mark.parametrize("body", ["collectives", "train_replicas", "torchmodel_overlap", "torchmodel_bn_vs_ddp"])
 def test_multi_gpu(body):
     _need_gpu()
     n = torch.cuda.device_count()
