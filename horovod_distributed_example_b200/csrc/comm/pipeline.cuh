@@ -95,3 +95,57 @@ __device__ __forceinline__ void hvd_param_wait_warp(const HvdParamWait& w) {
   // the weights were written by other GPUs' generic-proxy stores and are read next through TMA
   asm volatile("fence.proxy.async;" ::: "memory");
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// All-gather of the updated rows (step 3 above).  One "block" = a contiguous 1/nblk of this rank's rows, copied
+// to every other replica with plain 16-byte loads and peer stores (or multimem.st), then one version flag per
+// peer.  The same device function is (a) the stand-alone hvd_allgather_kernel used by flushes and (b) the role
+// of the FIRST blocks of the conv1 forward kernel of the next step: blocks of one grid are dispatched in index
+// order, so the copy starts with the step - a separate small kernel beside the conv forward was measured to
+// wait until that kernel's CTAs had all retired, whatever its stream priority.
+struct HvdAllgatherArgs {
+  long long w0, w1;               // the big tensor's range in the slab
+  long long param_off;            // slab offset of the parameters inside the arena buffer
+  const uint32_t* version[HVD_MAX_RANKS];   // [own rank]: device word written by the tail kernel
+  int use_mc;
+  unsigned long long* trace[HVD_MAX_RANKS];  // same ring as the tail's: [10] block 0 started, [11] block 0 stamped its flags
+};
+
+// `peer`: a __shared__ float*[HVD_MAX_RANKS] of the calling kernel.  Contains __syncthreads(): call from every
+// thread of the block.
+__device__ __forceinline__ void hvd_allgather_block(const HvdCommCtx& c, const HvdAllgatherArgs& a, float** peer, int blk,
+                                                    int nblk) {
+  const int rank = hvd_rank(c), N = c.nranks, tid = threadIdx.x, nt = blockDim.x;
+  const uint32_t v = *a.version[rank];
+  unsigned long long* tr = (a.trace[rank] && blk == 0 && tid == 0) ? a.trace[rank] + (size_t)(v & 63) * 16 : nullptr;
+  if (tr) tr[10] = globaltimer_ns();
+  const long long shard = (a.w1 - a.w0) / N;
+  const long long n4 = shard / 4;
+  const long long per = (n4 + nblk - 1) / nblk;
+  const long long i0 = (long long)blk * per, i1 = i0 + per < n4 ? i0 + per : n4;
+  const long long off = a.param_off + a.w0 + (long long)rank * shard;
+  const float* src = c.base[rank] + off;
+  if (tid < HVD_MAX_RANKS) peer[tid] = c.base[tid];
+  __syncthreads();
+  for (long long i = i0 + tid; i < i1; i += 4 * nt) {
+    float4 q[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (i + u * nt < i1) q[u] = ld_f4(src + (i + u * nt) * 4);
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      if (i + u * nt >= i1) continue;
+      const long long o = off + (i + u * nt) * 4;
+      if (a.use_mc) {
+        multimem_st_f4(c.mc_base + o, q[u]);          // also rewrites this rank's own copy with the same bits
+      } else {
+        for (int r = 0; r < N; r++)
+          if (r != rank) st_sys_f4(peer[r] + o, q[u]);
+      }
+    }
+  }
+  // every thread's stores happen-before the barrier; the release of the signalling threads is cumulative
+  __syncthreads();
+  if (tid < N && tid != rank) st_release_sys(hvd_flag(c, tid, HVD_SLOT_READY, blk, rank), v);
+  if (tr) tr[11] = globaltimer_ns();
+}

@@ -273,52 +273,12 @@ __global__ void __launch_bounds__(256, 2) hvd_tail_kernel(HvdCommCtx c, HvdTailA
 // synchronize alone does not cover stores that OTHER GPUs are still sending.
 __global__ void hvd_param_wait_kernel(HvdParamWait w) { hvd_param_wait_warp(w); }
 
-struct HvdAllgatherArgs {
-  long long w0, w1;               // the big tensor's range in the slab
-  long long param_off;            // slab offset of the parameters inside the arena buffer
-  const uint32_t* version[HVD_MAX_RANKS];   // [own rank]: device word written by the tail kernel
-  int use_mc;
-  unsigned long long* trace[HVD_MAX_RANKS];  // same ring as the tail's: [10] CTA 0 started, [11] CTA 0 stamped its flags
-};
-
 // Deliver this rank's rows of the big tensor to every other replica and stamp the version on every peer.
 // 128 threads, <= 32 registers: 4 K registers per CTA, which is what an SM has left beside a conv2 forward CTA.
 __global__ void __launch_bounds__(128, 16) hvd_allgather_kernel(HvdCommCtx c, HvdAllgatherArgs a) {
   asm volatile("griddepcontrol.wait;" ::: "memory");
-  const int rank = hvd_rank(c), N = c.nranks, tid = threadIdx.x;
-  const uint32_t v = *a.version[rank];
-  unsigned long long* tr = (a.trace[rank] && blockIdx.x == 0 && tid == 0) ? a.trace[rank] + (size_t)(v & 63) * 16 : nullptr;
-  if (tr) tr[10] = globaltimer_ns();
-  const long long shard = (a.w1 - a.w0) / N;
-  const long long n4 = shard / 4;
-  const long long per = (n4 + gridDim.x - 1) / gridDim.x;
-  const long long i0 = (long long)blockIdx.x * per, i1 = i0 + per < n4 ? i0 + per : n4;
-  const long long off = a.param_off + a.w0 + (long long)rank * shard;
-  const float* src = c.base[rank] + off;
   __shared__ float* peer[HVD_MAX_RANKS];       // shared memory, not registers: the kernel lives on 32 registers
-  if (tid < HVD_MAX_RANKS) peer[tid] = c.base[tid];
-  __syncthreads();
-  for (long long i = i0 + tid; i < i1; i += 4 * 128) {
-    float4 q[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-      if (i + u * 128 < i1) q[u] = ld_f4(src + (i + u * 128) * 4);
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      if (i + u * 128 >= i1) continue;
-      const long long o = off + (i + u * 128) * 4;
-      if (a.use_mc) {
-        multimem_st_f4(c.mc_base + o, q[u]);          // also rewrites this rank's own copy with the same bits
-      } else {
-        for (int r = 0; r < N; r++)
-          if (r != rank) st_sys_f4(peer[r] + o, q[u]);
-      }
-    }
-  }
-  // every thread's stores happen-before the barrier; the release of the signalling threads is cumulative
-  __syncthreads();
-  if (tid < N && tid != rank) st_release_sys(hvd_flag(c, tid, HVD_SLOT_READY, blockIdx.x, rank), v);
-  if (tr) tr[11] = globaltimer_ns();
+  hvd_allgather_block(c, a, peer, blockIdx.x, gridDim.x);
 }
 
 // The same delivery with the TMA engine doing the copying: ONE WARP per CTA, one lane issuing bulk copies

@@ -6,6 +6,7 @@
 //                 the whole backward of dense2 + the dropout/relu backward of dense1 in one CTA
 //                                                                          (mnist_keras.py:79-81,89-91)
 //   conv1_wgrad : dW/db of conv1 and db of conv2 (pure reductions)
+#include "comm/pipeline.cuh"
 #include "mnist_common.cuh"
 #include "tc_common.cuh"
 
@@ -24,14 +25,28 @@ struct Conv1Prologue {
   int advance_step;
 };
 
-__global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[9][32]*/,
+// Pipelined data-parallel step: the first `ag_blocks` blocks of this grid do not convolve - they deliver the rows
+// of dense_1/kernel this rank updated in the previous step to the other replicas (hvd_allgather_block), hidden
+// under the convolution the remaining blocks compute.
+struct Conv1Comm {
+  HvdCommCtx c;
+  HvdAllgatherArgs ag;
+  int ag_blocks;
+};
+
+__global__ void __launch_bounds__(256, 6) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[9][32]*/,
                                                         const float* __restrict__ bias, float* __restrict__ a1, int B,
-                                                        Conv1Prologue pro) {
+                                                        Conv1Prologue pro, const __grid_constant__ Conv1Comm comm) {
   __shared__ float sw[9 * 32 + 32];
   tc::pdl_launch_dependents();
   tc::pdl_wait();
+  if ((int)blockIdx.x < comm.ag_blocks) {
+    hvd_allgather_block(comm.c, comm.ag, reinterpret_cast<float**>(sw), blockIdx.x, comm.ag_blocks);
+    return;
+  }
+  const int cblk = blockIdx.x - comm.ag_blocks, cgrid = gridDim.x - comm.ag_blocks;
   {
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    const int gid = cblk * blockDim.x + threadIdx.x, gsz = cgrid * blockDim.x;
     for (int i = gid; i < pro.n_a / 4; i += gsz) reinterpret_cast<float4*>(pro.zero_a)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int i = gid; i < pro.n_b / 4; i += gsz) reinterpret_cast<float4*>(pro.zero_b)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (gid == 0 && pro.st) {
@@ -43,7 +58,7 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
   for (int i = threadIdx.x; i < 9 * 32 + 32; i += blockDim.x) sw[i] = i < 288 ? w[i] : bias[i - 288];
   __syncthreads();
   const long long total = (long long)B * H1 * H1 * 4;
-  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+  for (long long t = (long long)cblk * blockDim.x + threadIdx.x; t < total; t += (long long)cgrid * blockDim.x) {
     const int cg = (int)(t & 3);
     const long long pix = t >> 2;
     const int ox = (int)(pix % H1), oy = (int)((pix / H1) % H1);
@@ -268,21 +283,30 @@ __global__ void __launch_bounds__(256) colsum64_kernel(const float* __restrict__
 
 // blocks_per_sm (1..8): resident 256-thread CTAs per SM the grid is sized for.  8 fills every thread slot; the
 // pipelined multi-GPU step passes 7 so that the small all-gather CTAs enqueued beside it find a slot at once.
+// comm / ag / ag_blocks (may be NULL / 0): the all-gather role of the first ag_blocks blocks, see Conv1Comm.
 extern "C" int hvd_conv1_fwd_ex(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a,
                                 int n_a, float* zero_b, int n_b, void* step_state, int advance_step, void* stream,
-                                int blocks_per_sm) {
+                                int blocks_per_sm, const HvdCommCtx* comm, const HvdAllgatherArgs* ag, int ag_blocks) {
   if ((n_a | n_b) & 3) return -1;
   if (blocks_per_sm < 1 || blocks_per_sm > 8) return -2;
   const long long total = (long long)B * mnist::H1 * mnist::H1 * 4;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * blocks_per_sm) blocks = 148 * blocks_per_sm;
+  static Conv1Comm none;               // zero-initialised: ag_blocks = 0
+  Conv1Comm cc = none;
+  if (comm && ag && ag_blocks > 0) {
+    if (comm->nranks < 2 || ag_blocks > HVD_MAX_CTAS || (ag->use_mc && comm->mc_base == nullptr)) return -3;
+    cc.c = *comm; cc.ag = *ag; cc.ag_blocks = ag_blocks;
+    blocks += ag_blocks;
+  }
   Conv1Prologue pro{zero_a, zero_a ? n_a : 0, zero_b, zero_b ? n_b : 0, reinterpret_cast<mnist::StepState*>(step_state), advance_step};
-  return (int)tc::launch_pdl(conv1_fwd_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, w, bias, a1, B, pro);
+  return (int)tc::launch_pdl(conv1_fwd_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, w, bias, a1, B, pro, cc);
 }
 
 extern "C" int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a,
                              int n_a, float* zero_b, int n_b, void* step_state, int advance_step, void* stream) {
-  return hvd_conv1_fwd_ex(x, w, bias, a1, B, zero_a, n_a, zero_b, n_b, step_state, advance_step, stream, 8);
+  return hvd_conv1_fwd_ex(x, w, bias, a1, B, zero_a, n_a, zero_b, n_b, step_state, advance_step, stream, 8, nullptr,
+                          nullptr, 0);
 }
 
 extern "C" int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels,

@@ -45,7 +45,7 @@ def _declare(lib):
     lib.hvd_conv1_fwd.restype = ci
     lib.hvd_conv1_fwd.argtypes = [vp, vp, vp, vp, ci, vp, ci, vp, ci, vp, ci, vp]
     lib.hvd_conv1_fwd_ex.restype = ci
-    lib.hvd_conv1_fwd_ex.argtypes = [vp, vp, vp, vp, ci, vp, ci, vp, ci, vp, ci, vp, ci]
+    lib.hvd_conv1_fwd_ex.argtypes = [vp, vp, vp, vp, ci, vp, ci, vp, ci, vp, ci, vp, ci, vp, vp, ci]
     lib.hvd_conv2_fprop_ex.restype = ci
     lib.hvd_conv2_fprop_ex.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, cf, ci, vp, vp]
     lib.hvd_conv2_fprop.restype = ci
@@ -216,7 +216,10 @@ class MnistEngine:
         self._conv1_bps = 8
         self._tl_offset, self._tl_done, self._tl_active = None, 0, False
         self._hyper_pushed = False
-        self._ag_where = os.environ.get("HVD_AG_WHERE", "start")
+        # where the all-gather of the updated rows runs: "conv1" = as the first blocks of the next step's conv1
+        # forward kernel (default), "start" = a separate small kernel forked at the start of the next step,
+        # "tail" = right behind the tail kernel (exposed; A/B only)
+        self._ag_where = os.environ.get("HVD_AG_WHERE", "conv1")
         self._wait_in = os.environ.get("HVD_WAIT_IN", "fprop")
         self.side = torch.cuda.Stream(device=dev)
         self.side2 = torch.cuda.Stream(device=dev)
@@ -272,8 +275,7 @@ class MnistEngine:
                                                ctas=int(os.environ.get("HVD_TAIL_CTAS", 0)) or None,
                                                ag_ctas=int(os.environ.get("HVD_AG_CTAS", 0)) or None)
             opt._pipe = self.pipe             # checkpoints gather the owner-sharded state through it
-            if self.pipe.n > 1:               # leave thread slots for the all-gather CTAs that start with conv1
-                self._conv1_bps = int(os.environ.get("HVD_CONV1_BPS", 7))
+            self._conv1_bps = int(os.environ.get("HVD_CONV1_BPS", 8))
             if os.environ.get("HVD_TAIL_TRACE", "0") == "1" or basics.state().timeline is not None:
                 self.pipe.enable_trace()
             if basics.state().timeline is not None:
@@ -392,10 +394,17 @@ class MnistEngine:
             za, zb = g.data_ptr(), g.data_ptr() + 4 * first_conv
         xin = self.x_bufs[which or 0]
         if "conv1_fwd" not in self._SKIP:
+            cc = ag = None
+            agb = 0
+            if which is not None and self.pipe is not None and self.pipe.n > 1 and self._ag_where == "conv1":
+                # the first blocks of this kernel deliver last step's updated rows of dense_1/kernel to the peers
+                cc = ctypes.addressof(self.pipe.ctx.comm_ctx(self.pipe.buf))
+                ag = ctypes.addressof(self.pipe.allgather_args())
+                agb = self.pipe.ag_ctas
             self._chk(lib.hvd_conv1_fwd_ex(xin.data_ptr(), self._p("c1", "kernel").data_ptr(),
                                            self._p("c1", "bias").data_ptr(), self.a1.data_ptr(), B, za, na, zb, nb,
                                            self.state.data_ptr(), int(which is not None), s,
-                                           self._conv1_bps if which is not None else 8), "conv1_fwd")
+                                           self._conv1_bps if which is not None else 8, cc, ag, agb), "conv1_fwd")
         if "fprop" not in self._SKIP:
             # pipelined mode: CTA 0's spare warp also waits for the peers' rows of dense_1/kernel, so the Dense
             # forward behind this kernel starts with the weights already delivered (HVD_WAIT_IN=d1fwd moves it back)

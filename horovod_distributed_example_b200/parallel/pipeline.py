@@ -108,7 +108,7 @@ class PipelinedStep:
         self._versions = [torch.zeros(1, dtype=torch.int32, device=ctx.device) for _ in range(n_local)]
         # all-gather CTAs: ~36 KB of rows each, at most 256 (rank, CTA) delivery flags for the readers to check
         shard_bytes = self.shard * 4
-        self.ag_ctas = ag_ctas or max(8, min(32, 256 // max(n, 1), (shard_bytes + 16383) // 16384))
+        self.ag_ctas = ag_ctas or max(8, min(64, 256 // max(n, 1), (shard_bytes + 16383) // 16384))
         # One CTA per SM: 256-thread CTAs, the LL part wants one packet per thread, the rest stream the shard
         self.ll_ctas = ll_ctas or max(1, min(64, (self.npk + 255) // 256))
         total = ctas or 296                # two 256-thread CTAs per SM: the shard part is a bandwidth-bound stream
@@ -242,11 +242,7 @@ class PipelinedStep:
             msg = self.lib.hvd_cuda_error_string(rc).decode() if rc > 0 else f"bad arguments ({rc})"
             raise RuntimeError(f"hvd_tail_launch failed: {msg}")
 
-    def launch_allgather(self, stream=None) -> None:
-        """Deliver this rank's rows of the big tensor (current version) to every other replica.  Idempotent;
-        enqueued at the start of every training step and by ``flush``.  No-op at size 1."""
-        if self.n == 1:
-            return
+    def allgather_args(self) -> HvdAllgatherArgs:
         a = self._ag_args
         if a is None:
             a = self._ag_args = HvdAllgatherArgs()
@@ -256,6 +252,15 @@ class PipelinedStep:
                 a.version[r] = self._versions[self._rank_index(r)].data_ptr()
                 a.trace[r] = self._trace[self._rank_index(r)].data_ptr() if self._trace is not None else None
             a.use_mc = int(self.use_mc)
+        return a
+
+    def launch_allgather(self, stream=None) -> None:
+        """Deliver this rank's rows of the big tensor (current version) to every other replica.  Idempotent;
+        used by ``flush`` (inside a training step the first blocks of the conv1 forward kernel do the same
+        through ``allgather_args``).  No-op at size 1."""
+        if self.n == 1:
+            return
+        a = self.allgather_args()
         rc = self.lib.hvd_allgather_launch(ctypes.byref(self.ctx.comm_ctx(self.buf)), ctypes.byref(a), self.ag_ctas,
                                            self.ctx._stream(stream), self.n if self.ctx.emulated else 0,
                                            int(self.ag_tma))
