@@ -130,7 +130,7 @@ def main():
                 nvls_min = row["bytes"]
             cta_tab.append([row["bytes"], row[best + "_ctas"]])
         out = {"n_gpus": n, "nvls": has_nvls, "rows": rows,
-               "table": {str(n): {"oneshot_max_bytes": one_max, "nvls_min_bytes": nvls_min or one_max * 4,
+               "table": {str(n): {"oneshot_max_bytes": one_max, "nvls_min_bytes": nvls_min or (1 << 62),      # never won: never picked
                                   "ctas": cta_tab}}}
         os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
         json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"allreduce_sweep_N{n}.json"), "w"), indent=1)
