@@ -519,7 +519,10 @@ def stock_loop(args):
     if n > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     clocks = sampler.stop()
-    # e2e: pinned host batch -> device every step, loss.item() every step
+    # e2e: pinned host batch -> device every step, loss.item() every step (3 untimed steps first: the first
+    # host-fed steps of this arm pay one-off allocator / cuDNN work that a 20-step run would otherwise carry)
+    for i in range(3):
+        step(xs_host[i].to(dev, non_blocking=True), ys_host[i].to(dev, non_blocking=True)).item()
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):

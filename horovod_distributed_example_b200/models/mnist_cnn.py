@@ -1,24 +1,34 @@
 """The fused MNIST-CNN engine: the reference's flagship model (``mnist_keras.py:71-81``,
 ``tensorflow2_keras_mnist.py:43-52``) as a CUDA-graph-captured chain of hand-written sm_100a
-kernels.  Selected automatically by ``Model.compile`` when the layer stack matches.
+kernels.  Selected automatically by ``Model.compile`` when the layer stack matches (a model that does
+not match logs a WARNING and runs on torch autograd).
 
-One training step = 11 launches replayed from a CUDA graph (no Python per layer, no host sync):
+One training step = ONE graph replay of 9 launches (10 at size > 1), no Python per layer, no host sync:
 
-    conv1_fwd (CUDA cores, K=9)                          csrc/kernels/mnist_small.cu
-    conv2_fprop   tcgen05 implicit GEMM + bias/ReLU/maxpool/dropout epilogue   conv2_fprop.cu
-    dense1 fwd    tcgen05 split-K GEMM (x[B,9216] * W[9216,128])              tc_gemm.cu
-    head          bias/ReLU/dropout, Dense(10)+softmax+CE+accuracy, dense2 backward, dense1 mask bwd
+    conv1_fwd     CUDA cores, K=9; also the step prologue (zeroes the red.add gradient ranges); at size > 1
+                  its first blocks deliver last step's updated rows of dense_1/kernel to the other replicas
+    conv2_fprop   tcgen05 implicit GEMM + bias/ReLU/maxpool/dropout epilogue; a spare warp of CTA 0 waits for
+                  the peers' rows of dense_1/kernel (version flags) so that nothing else has to
+    dense1 fwd    tcgen05 split-K GEMM (x[B,9216] * W[9216,128])                              tc_gemm.cu
+    head          bias/ReLU/dropout, Dense(10)+softmax+CE+accuracy, dense2 backward, dense1 mask backward
     dense1 dX     tcgen05 GEMM + maxpool/dropout/ReLU-backward scatter epilogue (EPI_UNPOOL)
-    dense1 dW     tcgen05 GEMM (both operands MN-major) -> written straight into the grad arena
-       -> bucket 0 (98% of the bytes) starts its fused allreduce+update on a side stream here
-    conv2_dgrad   tcgen05 implicit GEMM, zero padding by TMA OOB fill, ReLU-backward epilogue, and conv1's
+    dense1 dW     tcgen05 GEMM (both operands MN-major) whose epilogue PUSHES every 128-row tile into the receive
+                  area of the rank that owns those rows (EPI_RS_PUSH: GEMM -> reduce-scatter in one kernel,
+                  over peer memory), on its own stream under dX and the conv backward; a 1-CTA kernel behind
+                  it raises the per-tile flags (size > 1)
+    conv2_dgrad   tcgen05 implicit GEMM, zero padding by TMA OOB fill, ReLU-backward epilogue, conv1's
                   weight/bias gradient as a second tensor-core GEMM over tiles staged by the epilogue
-    conv2_wgrad   tcgen05 split-K over pixels (+ column-sum kernel for the bias gradient, side branch)
-    fused allreduce + 1/N + Adadelta/Adam update, bucket 0 and bucket 1   csrc/comm/fused_allreduce.cu
+    conv2_wgrad   tcgen05, one N=192 MMA per input row covers all nine taps; conv2 bias gradient; CTA 0
+                  publishes (loss, accuracy, step) to a page-locked host ring
+    tail          csrc/comm/pipeline_tail.cu: barrier-free LL one-shot allreduce + update of the ~80 KB of small
+                  tensors, and the owner's reduce + update of its rows of dense_1/kernel (state sharded by owner)
 
-Gradients are double-buffered across steps at size > 1 (two captured graphs), which removes the
-one-shot kernel's exit barrier.  Loss/accuracy stay on the device: the head kernel
-writes them into a state block the trainer reads lazily.
+(``HVD_BUCKET_MODE=tail|overlap`` keeps round 1's bucket kernels - ``fused_allreduce.cu`` - selectable; world
+sizes that do not divide the 72 row tiles, and ``HVD_DEBUG_POISON``, use them automatically.)
+
+Gradients, inputs and hyper-parameter rows are double-buffered by step parity (two captured graphs).
+Loss/accuracy stay on the device: the head kernel writes them into a state block, the wgrad kernel
+copies them to the host ring, and the trainer reads them lazily.
 """
 from __future__ import annotations
 

@@ -120,6 +120,39 @@ int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int N, int K, i
                 int epilogue, const float* bias, long long ldd, void* stream, unsigned lbo_a, unsigned sbo_a,
                 unsigned lbo_b, unsigned sbo_b, const uint8_t* mask, float scale);
 
+/* Same GEMM with the two hooks of the pipelined data-parallel step (csrc/comm/pipeline.cuh; either may be NULL):
+ * rs   - epilogue 4 (EPI_RS_PUSH): every 128x128 output tile is written into the receive area of the rank that
+ *        owns those rows, local memory or a peer GPU over NVLink (D may be NULL) - the Dense(128) weight gradient's
+ *        reduce-scatter fused into the GEMM that produces it (hvd.DistributedOptimizer, reference mnist_keras.py:87);
+ * wait - the producer warp first waits for the version flags of the weights it is about to read. */
+struct HvdRsPush;
+struct HvdParamWait;
+struct HvdTailArgs;
+struct HvdAllgatherArgs;
+struct HvdLLArgs;
+int hvd_tc_gemm_ex(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn, int bn, int k_split,
+                   int epilogue, const float* bias, long long ldd, void* stream, unsigned lbo_a, unsigned sbo_a,
+                   unsigned lbo_b, unsigned sbo_b, const uint8_t* mask, float scale, const struct HvdRsPush* rs,
+                   const struct HvdParamWait* wait);
+
+/* Pipelined data-parallel step (csrc/comm/pipeline_tail.cu) - what hvd.DistributedOptimizer's allreduce + 1/N +
+ * optimizer update (reference mnist_keras.py:84-87, tensorflow2_keras_mnist.py:55-58) becomes on the fused engine.
+ * hvd_rs_flags_launch: raise the "tile landed" flags of the EPI_RS_PUSH GEMM just enqueued on `stream`.
+ * hvd_tail_launch: LL one-shot allreduce + update of the small tensors and the owner's reduce + update of its rows.
+ * hvd_allgather_launch: deliver the owned rows to every replica and stamp version flags (use_tma: TMA bulk copies).
+ * hvd_param_wait_launch: make `stream` wait until every peer's rows of the current version have landed.
+ * emulate_ranks > 0: all ranks on one GPU (tests); the tail then runs as one cooperative launch. */
+int hvd_rs_flags_launch(const struct HvdRsPush* rs, void* stream);
+int hvd_tail_launch(const struct HvdCommCtx* c, const struct HvdTailArgs* a, int ctas, void* stream, int emulate_ranks);
+int hvd_allgather_launch(const struct HvdCommCtx* c, const struct HvdAllgatherArgs* a, int ctas, void* stream,
+                         int emulate_ranks, int use_tma);
+int hvd_param_wait_launch(const struct HvdParamWait* w, void* stream);
+int hvd_globaltimer_probe(unsigned long long* out, void* stream);   /* one %globaltimer reading (HVD_TIMELINE calibration) */
+/* Barrier-free LL one-shot allreduce of a small message (<= 128 KB by default): flagged 16-byte packets pushed to
+ * every peer, no barrier.  The packed metric vector of MetricAverageCallback (reference tensorflow2_keras_mnist.py:77)
+ * and any small tensor-level hvd.allreduce. */
+int hvd_ll_allreduce_launch(const struct HvdCommCtx* c, const struct HvdLLArgs* a, void* stream, int emulate_ranks);
+
 /* Fused MNIST-CNN engine kernels (reference model mnist_keras.py:71-81). */
 /* conv1 forward; also the step prologue: clears [zero_a, +n_a) and [zero_b, +n_b) (the gradient ranges
  * later kernels red.add into; multiples of 4 floats, may be NULL), clears the per-step loss/accuracy words
@@ -128,6 +161,15 @@ int hvd_conv1_fwd(const float* x, const float* w, const float* bias, float* a1, 
                   float* zero_b, int n_b, void* step_state, int advance_step, void* stream);
 int hvd_conv2_fprop(const float* a1, const float* w2, const float* bias2, float* p2, uint8_t* mask,
                     const void* step_state, int B, int training, float keep, int ctas, void* stream);
+/* _ex variants for the pipelined step: conv1's grid is sized for blocks_per_sm resident blocks and its first
+ * ag_blocks blocks deliver last step's updated Dense(128) rows to the peers (comm / ag may be NULL, ag_blocks 0);
+ * conv2's spare warp waits for the peers' rows (wait may be NULL). */
+int hvd_conv1_fwd_ex(const float* x, const float* w, const float* bias, float* a1, int B, float* zero_a, int n_a,
+                     float* zero_b, int n_b, void* step_state, int advance_step, void* stream, int blocks_per_sm,
+                     const struct HvdCommCtx* comm, const struct HvdAllgatherArgs* ag, int ag_blocks);
+int hvd_conv2_fprop_ex(const float* a1, const float* w2, const float* bias2, float* p2, uint8_t* mask,
+                       const void* step_state, int B, int training, float keep, int ctas, void* stream,
+                       const struct HvdParamWait* wait);
 /* g_w2 / g_b2 / g_b1 and the loss/accuracy words are ACCUMULATED into (zeroed by hvd_conv1_fwd's prologue). */
 int hvd_head(float* h_pre, const float* b1, const float* w2, const float* b2, const long long* labels, float* dh_pre,
              float* g_w2, float* g_b2, float* g_b1, float* probs, void* step_state, int B, int training, int backward,
