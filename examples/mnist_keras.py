@@ -32,14 +32,18 @@ def load_data():
         xte, yte = xte[:max(limit // 4, 256)], yte[:max(limit // 4, 256)]
 
     def prep(x):
-        return (x.reshape(len(x), 28, 28, 1).astype("float32")) / 255
+        # both input layouts of the reference (mnist_keras.py:50-57); channels_last is the default and the one
+        # the fused sm_100a engine runs, channels_first trains on the torch-autograd backend
+        shape = (1, 28, 28) if keras.backend.image_data_format() == "channels_first" else (28, 28, 1)
+        return (x.reshape(len(x), *shape).astype("float32")) / 255
 
     return (prep(xtr), keras.utils.to_categorical(ytr, CLASSES)), (prep(xte), keras.utils.to_categorical(yte, CLASSES))
 
 
 def build_model():
     return keras.Sequential([
-        keras.layers.Conv2D(32, (3, 3), activation="relu", input_shape=(28, 28, 1)),
+        keras.layers.Conv2D(32, (3, 3), activation="relu",
+                            input_shape=(1, 28, 28) if keras.backend.image_data_format() == "channels_first" else (28, 28, 1)),
         keras.layers.Conv2D(64, (3, 3), activation="relu"),
         keras.layers.MaxPooling2D((2, 2)),
         keras.layers.Dropout(0.25),

@@ -4,8 +4,7 @@ from .models import clear_session  # noqa: F401
 _learning_phase = 1
 
 
-def image_data_format() -> str:
-    return "channels_last"
+from .layers import image_data_format, set_image_data_format  # noqa: F401,E402
 
 
 def set_learning_phase(value: int) -> None:

@@ -41,6 +41,29 @@ def glorot_uniform(shape, fan_in, fan_out, generator=None):
     return (torch.rand(shape, generator=generator) * 2.0 - 1.0) * limit
 
 
+# keras.backend.image_data_format(): 'channels_last' (default, what the fused engine runs) or 'channels_first'
+# (the reference's other input branch, mnist_keras.py:50-53; runs on the torch-autograd backend)
+_image_data_format = "channels_last"
+
+
+def image_data_format() -> str:
+    return _image_data_format
+
+
+def set_image_data_format(fmt: str) -> None:
+    global _image_data_format
+    if fmt not in ("channels_last", "channels_first"):
+        raise ValueError("data_format must be 'channels_last' or 'channels_first'")
+    _image_data_format = fmt
+
+
+def _fmt(data_format):
+    f = data_format or _image_data_format
+    if f not in ("channels_last", "channels_first"):
+        raise ValueError("data_format must be 'channels_last' or 'channels_first'")
+    return f
+
+
 class Layer:
     """Base layer.  Subclasses define ``build`` (returns weight specs + output shape)
     and ``call``."""
@@ -90,8 +113,9 @@ class Conv2D(Layer):
     base_name = "conv2d"
 
     def __init__(self, filters, kernel_size, strides=(1, 1), padding="valid", activation=None,
-                 use_bias=True, **kw):
+                 use_bias=True, data_format=None, **kw):
         super().__init__(**kw)
+        self.data_format = _fmt(data_format)
         self.filters = int(filters)
         self.kernel_size = _pair(kernel_size)
         self.strides = _pair(strides)
@@ -102,16 +126,19 @@ class Conv2D(Layer):
         self.use_bias = use_bias
 
     def compute_output_shape(self, s):
-        h, w, _ = s
+        cf = self.data_format == "channels_first"
+        h, w = (s[1], s[2]) if cf else (s[0], s[1])
         kh, kw = self.kernel_size
         sh, sw = self.strides
         if self.padding == "valid":
-            return ((h - kh) // sh + 1, (w - kw) // sw + 1, self.filters)
-        return (math.ceil(h / sh), math.ceil(w / sw), self.filters)
+            oh, ow = (h - kh) // sh + 1, (w - kw) // sw + 1
+        else:
+            oh, ow = math.ceil(h / sh), math.ceil(w / sw)
+        return (self.filters, oh, ow) if cf else (oh, ow, self.filters)
 
     def build(self, input_shape):
         super().build(input_shape)
-        cin = input_shape[-1]
+        cin = input_shape[0] if self.data_format == "channels_first" else input_shape[-1]
         kh, kw = self.kernel_size
         fan_in, fan_out = kh * kw * cin, kh * kw * self.filters
         specs = [("kernel", (kh, kw, cin, self.filters),
@@ -125,19 +152,21 @@ class Conv2D(Layer):
         # matter here: this is the oracle path)
         w = self.weights["kernel"].permute(3, 2, 0, 1)
         b = self.weights.get("bias")
-        xin = x.permute(0, 3, 1, 2)
+        cf = self.data_format == "channels_first"
+        xin = x if cf else x.permute(0, 3, 1, 2)
         if self.padding == "same":
             kh, kw = self.kernel_size
             ph, pw = kh - 1, kw - 1
             xin = F.pad(xin, (pw // 2, pw - pw // 2, ph // 2, ph - ph // 2))
         y = F.conv2d(xin, w, b, stride=self.strides)
-        y = y.permute(0, 2, 3, 1)
+        if not cf:
+            y = y.permute(0, 2, 3, 1)
         return _ACTIVATIONS[self.activation](y)
 
     def get_config(self):
         return {"name": self.name, "trainable": True, "filters": self.filters,
                 "kernel_size": list(self.kernel_size), "strides": list(self.strides),
-                "padding": self.padding, "data_format": "channels_last",
+                "padding": self.padding, "data_format": self.data_format,
                 "dilation_rate": [1, 1], "activation": self.activation or "linear",
                 "use_bias": self.use_bias,
                 "kernel_initializer": {"class_name": "VarianceScaling", "config": {
@@ -150,33 +179,37 @@ class Conv2D(Layer):
 class MaxPooling2D(Layer):
     base_name = "max_pooling2d"
 
-    def __init__(self, pool_size=(2, 2), strides=None, padding="valid", **kw):
+    def __init__(self, pool_size=(2, 2), strides=None, padding="valid", data_format=None, **kw):
         super().__init__(**kw)
+        self.data_format = _fmt(data_format)
         self.pool_size = _pair(pool_size)
         self.strides = _pair(strides) if strides is not None else self.pool_size
         self.padding = padding.lower()
 
     def compute_output_shape(self, s):
-        h, w, c = s
-        return ((h - self.pool_size[0]) // self.strides[0] + 1,
-                (w - self.pool_size[1]) // self.strides[1] + 1, c)
+        cf = self.data_format == "channels_first"
+        c, h, w = (s[0], s[1], s[2]) if cf else (s[2], s[0], s[1])
+        oh = (h - self.pool_size[0]) // self.strides[0] + 1
+        ow = (w - self.pool_size[1]) // self.strides[1] + 1
+        return (c, oh, ow) if cf else (oh, ow, c)
+
+    _pool = staticmethod(F.max_pool2d)
 
     def call(self, x, training, rng=None):
-        y = F.max_pool2d(x.permute(0, 3, 1, 2), self.pool_size, self.strides)
+        if self.data_format == "channels_first":
+            return self._pool(x, self.pool_size, self.strides)
+        y = self._pool(x.permute(0, 3, 1, 2), self.pool_size, self.strides)
         return y.permute(0, 2, 3, 1)
 
     def get_config(self):
         return {"name": self.name, "trainable": True, "pool_size": list(self.pool_size),
                 "padding": self.padding, "strides": list(self.strides),
-                "data_format": "channels_last"}
+                "data_format": self.data_format}
 
 
 class AveragePooling2D(MaxPooling2D):
     base_name = "average_pooling2d"
-
-    def call(self, x, training, rng=None):
-        y = F.avg_pool2d(x.permute(0, 3, 1, 2), self.pool_size, self.strides)
-        return y.permute(0, 2, 3, 1)
+    _pool = staticmethod(F.avg_pool2d)
 
 
 class GlobalAveragePooling2D(Layer):
@@ -219,11 +252,17 @@ class Flatten(Layer):
             n *= d
         return (n,)
 
+    def __init__(self, data_format=None, **kw):
+        super().__init__(**kw)
+        self.data_format = _fmt(data_format)
+
     def call(self, x, training, rng=None):
+        if self.data_format == "channels_first" and x.ndim == 4:
+            x = x.permute(0, 2, 3, 1)        # Keras: channels_first inputs are flattened in channels_last order
         return x.reshape(x.shape[0], -1)     # NHWC -> (h, w, c) order, as Keras
 
     def get_config(self):
-        return {"name": self.name, "trainable": True, "data_format": "channels_last"}
+        return {"name": self.name, "trainable": True, "data_format": self.data_format}
 
 
 class Dense(Layer):
@@ -292,10 +331,12 @@ def from_config(class_name: str, config: Dict) -> Layer:
         return Conv2D(c["filters"], tuple(c["kernel_size"]), tuple(c.get("strides", (1, 1))),
                       c.get("padding", "valid"),
                       None if c.get("activation") == "linear" else c.get("activation"),
-                      c.get("use_bias", True), **kw)
+                      c.get("use_bias", True), data_format=c.get("data_format"), **kw)
     if cls in (MaxPooling2D, AveragePooling2D):
         return cls(tuple(c["pool_size"]), tuple(c["strides"]) if c.get("strides") else None,
-                   c.get("padding", "valid"), **kw)
+                   c.get("padding", "valid"), data_format=c.get("data_format"), **kw)
+    if cls is Flatten:
+        return Flatten(data_format=c.get("data_format"), **kw)
     if cls is Dropout:
         return Dropout(c["rate"], **kw)
     if cls is Dense:

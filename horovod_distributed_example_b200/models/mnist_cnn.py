@@ -87,6 +87,8 @@ def matches(model) -> bool:
     if not ls or len(ls) != 8 or tuple(model.input_shape) != (28, 28, 1):
         return False
     c1, c2, mp, d1, fl, f1, d2, f2 = ls
+    if any(getattr(l, "data_format", "channels_last") != "channels_last" for l in ls):
+        return False
     ok = (isinstance(c1, L.Conv2D) and c1.filters == 32 and c1.kernel_size == (3, 3) and c1.activation == "relu"
           and c1.padding == "valid" and c1.strides == (1, 1) and c1.use_bias
           and isinstance(c2, L.Conv2D) and c2.filters == 64 and c2.kernel_size == (3, 3) and c2.activation == "relu"

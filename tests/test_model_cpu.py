@@ -124,3 +124,28 @@ def test_torchmodel_resnet_tiny_trains_through_arena(hvd_single):
     from horovod_distributed_example_b200.parallel import buckets as B
     bk = B.plan(m.arena, 16 << 10)
     assert len(bk) > 3 and bk[0].start == 0 and bk[-1].end == m.arena.n
+
+
+def test_channels_first_matches_channels_last():
+    """The reference's other input branch (mnist_keras.py:50-53): the same weights give the same outputs whether
+    the images arrive as (N,1,28,28) or (N,28,28,1); Flatten keeps the (h,w,c) order in both."""
+    rng = np.random.default_rng(3)
+    x = rng.random((4, 28, 28, 1), dtype=np.float32)
+    m_last = _model(seed=5); m_last.build()
+    keras.backend.set_image_data_format("channels_first")
+    try:
+        assert keras.backend.image_data_format() == "channels_first"
+        keras.backend.clear_session()
+        m_first = keras.Sequential([
+            keras.layers.Conv2D(32, (3, 3), activation='relu', input_shape=(1, 28, 28)),
+            keras.layers.Conv2D(64, (3, 3), activation='relu'), keras.layers.MaxPooling2D((2, 2)),
+            keras.layers.Dropout(0.25), keras.layers.Flatten(), keras.layers.Dense(128, activation='relu'),
+            keras.layers.Dropout(0.5), keras.layers.Dense(10, activation='softmax')], seed=5)
+        m_first.build()
+        assert [l.output_shape for l in m_first.layers][:3] == [(32, 26, 26), (64, 24, 24), (64, 12, 12)]
+        m_first.set_weights(m_last.get_weights())
+        p1 = m_first.predict(np.ascontiguousarray(x.transpose(0, 3, 1, 2)))
+    finally:
+        keras.backend.set_image_data_format("channels_last")
+    np.testing.assert_allclose(p1, m_last.predict(x), rtol=1e-5, atol=1e-6)
+    assert m_first.get_config()["layers"][0]["config"]["data_format"] == "channels_first"
