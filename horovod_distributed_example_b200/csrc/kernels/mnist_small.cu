@@ -34,7 +34,7 @@ struct Conv1Comm {
   int ag_blocks;
 };
 
-__global__ void __launch_bounds__(256, 6) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[9][32]*/,
+__global__ void __launch_bounds__(256, 5) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[9][32]*/,
                                                         const float* __restrict__ bias, float* __restrict__ a1, int B,
                                                         Conv1Prologue pro, const __grid_constant__ Conv1Comm comm) {
   __shared__ float sw[9 * 32 + 32];
@@ -57,29 +57,46 @@ __global__ void __launch_bounds__(256, 6) conv1_fwd_kernel(const float* __restri
   }
   for (int i = threadIdx.x; i < 9 * 32 + 32; i += blockDim.x) sw[i] = i < 288 ? w[i] : bias[i - 288];
   __syncthreads();
+  // Two work items per thread, both items' loads issued before either is used, and a grid of ONE wave (676 CTAs
+  // at batch 128, five resident per SM): with one item per thread the 346 K items needed a partial second round
+  // on the 303 K resident threads, i.e. two dependent load-compute-store latencies instead of one.
   const long long total = (long long)B * H1 * H1 * 4;
-  for (long long t = (long long)cblk * blockDim.x + threadIdx.x; t < total; t += (long long)cgrid * blockDim.x) {
-    const int cg = (int)(t & 3);
-    const long long pix = t >> 2;
-    const int ox = (int)(pix % H1), oy = (int)((pix / H1) % H1);
-    const int b = (int)(pix / (H1 * H1));
-    const float* xi = x + ((long long)b * IMG + oy) * IMG + ox;
-    float in[9];
+  const long long half = (total + 1) / 2;
+  for (long long t0 = (long long)cblk * blockDim.x + threadIdx.x; t0 < half; t0 += (long long)cgrid * blockDim.x) {
+    float in[2][9];
+    long long pixs[2];
+    int cgs[2];
+    bool on[2];
 #pragma unroll
-    for (int kh = 0; kh < 3; kh++)
+    for (int u = 0; u < 2; u++) {
+      const long long t = t0 + u * half;
+      on[u] = t < total;
+      const long long tt = on[u] ? t : 0;
+      cgs[u] = (int)(tt & 3);
+      pixs[u] = tt >> 2;
+      const int ox = (int)(pixs[u] % H1), oy = (int)((pixs[u] / H1) % H1);
+      const int b = (int)(pixs[u] / (H1 * H1));
+      const float* xi = x + ((long long)b * IMG + oy) * IMG + ox;
 #pragma unroll
-      for (int kw = 0; kw < 3; kw++) in[kh * 3 + kw] = __ldg(xi + kh * IMG + kw);
-    float o[8];
+      for (int kh = 0; kh < 3; kh++)
 #pragma unroll
-    for (int c = 0; c < 8; c++) {
-      float acc = sw[288 + cg * 8 + c];
-#pragma unroll
-      for (int k = 0; k < 9; k++) acc = fmaf(in[k], sw[k * 32 + cg * 8 + c], acc);
-      o[c] = fmaxf(acc, 0.f);
+        for (int kw = 0; kw < 3; kw++) in[u][kh * 3 + kw] = __ldg(xi + kh * IMG + kw);
     }
-    float4* dst = reinterpret_cast<float4*>(a1 + pix * C1 + cg * 8);
-    dst[0] = make_float4(o[0], o[1], o[2], o[3]);
-    dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      if (!on[u]) continue;
+      float o[8];
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        float acc = sw[288 + cgs[u] * 8 + c];
+#pragma unroll
+        for (int k = 0; k < 9; k++) acc = fmaf(in[u][k], sw[k * 32 + cgs[u] * 8 + c], acc);
+        o[c] = fmaxf(acc, 0.f);
+      }
+      float4* dst = reinterpret_cast<float4*>(a1 + pixs[u] * C1 + cgs[u] * 8);
+      dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+      dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+    }
   }
 }
 
@@ -290,7 +307,7 @@ extern "C" int hvd_conv1_fwd_ex(const float* x, const float* w, const float* bia
   if ((n_a | n_b) & 3) return -1;
   if (blocks_per_sm < 1 || blocks_per_sm > 8) return -2;
   const long long total = (long long)B * mnist::H1 * mnist::H1 * 4;
-  int blocks = (int)((total + 255) / 256);
+  int blocks = (int)(((total + 1) / 2 + 255) / 256);          // two work items per thread
   if (blocks > 148 * blocks_per_sm) blocks = 148 * blocks_per_sm;
   static Conv1Comm none;               // zero-initialised: ag_blocks = 0
   Conv1Comm cc = none;
