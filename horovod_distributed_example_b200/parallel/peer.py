@@ -20,10 +20,8 @@ GPU are not safe (B200_PROFILING.md).
 """
 from __future__ import annotations
 
-import array
 import ctypes
 import os
-import socket
 import tempfile
 from typing import List, Optional
 
@@ -149,38 +147,57 @@ def _declare_symm(core):
     core._hvd_symm_declared = True
 
 
+class HvdBootMsg(ctypes.Structure):
+    _fields_ = [("magic", ctypes.c_uint32), ("version", ctypes.c_uint16), ("kind", ctypes.c_uint16),
+                ("src_rank", ctypes.c_int32), ("tag", ctypes.c_int32), ("payload", ctypes.c_uint64)]
+
+
+BOOT_KIND_MEM, BOOT_KIND_MC = 1, 2
+
+
+def _declare_boot(core):
+    if getattr(core, "_hvd_boot_declared", False):
+        return
+    core.hvd_boot_open.restype = ctypes.c_void_p
+    core.hvd_boot_open.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_double]
+    core.hvd_boot_send.restype = ctypes.c_int
+    core.hvd_boot_send.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_uint64, ctypes.c_int]
+    core.hvd_boot_recv.restype = ctypes.c_int
+    core.hvd_boot_recv.argtypes = [ctypes.c_void_p, ctypes.POINTER(HvdBootMsg), ctypes.POINTER(ctypes.c_int)]
+    core.hvd_boot_close.argtypes = [ctypes.c_void_p]
+    core.hvd_boot_last_error.restype = ctypes.c_char_p
+    core._hvd_boot_declared = True
+
+
 class _FdExchange:
-    """All-to-all exchange of POSIX fds between the ranks of one host (SCM_RIGHTS)."""
+    """All-to-all exchange of POSIX fds between the ranks of one host: the native bootstrap channel
+    (``csrc/core/bootstrap.cpp``: fixed-layout ``HvdBootMsg`` + SCM_RIGHTS over unix datagram sockets)."""
 
-    def __init__(self, rank: int, size: int, tag: str):
+    def __init__(self, rank: int, size: int, tag: str, timeout_s: float = 60.0):
         self.rank, self.size = rank, size
+        self.core = native.core_lib()
+        _declare_boot(self.core)
         self.dir = os.path.join(tempfile.gettempdir(), f"hvd-symm-{tag}")
-        os.makedirs(self.dir, exist_ok=True)
-        self.path = os.path.join(self.dir, f"r{rank}.sock")
-        if os.path.exists(self.path):
-            os.unlink(self.path)
-        self.sock = socket.socket(socket.AF_UNIX, socket.SOCK_DGRAM)
-        self.sock.bind(self.path)
-        self.sock.settimeout(60.0)
+        self.h = self.core.hvd_boot_open(self.dir.encode(), rank, size, float(timeout_s))
+        if not self.h:
+            raise RuntimeError(f"bootstrap channel: {self.core.hvd_boot_last_error().decode()}")
 
-    def _peer(self, r: int) -> str:
-        return os.path.join(self.dir, f"r{r}.sock")
-
-    def send(self, dst: int, fd: int, tag: int):
-        # socket.send_fds() drops its `address` argument on this Python; call sendmsg directly
-        self.sock.sendmsg([tag.to_bytes(4, "little") + self.rank.to_bytes(4, "little")],
-                          [(socket.SOL_SOCKET, socket.SCM_RIGHTS, array.array("i", [fd]))], 0, self._peer(dst))
+    def send(self, dst: int, fd: int, tag: int, kind: int = BOOT_KIND_MEM, payload: int = 0):
+        if self.core.hvd_boot_send(self.h, dst, kind, tag, payload, fd) != 0:
+            raise RuntimeError(f"bootstrap send to rank {dst}: {self.core.hvd_boot_last_error().decode()}")
 
     def recv(self):
-        msg, fds, _flags, _addr = socket.recv_fds(self.sock, 8, 1)
-        return int.from_bytes(msg[:4], "little"), int.from_bytes(msg[4:8], "little"), fds[0]
+        """-> (tag, source rank, fd)"""
+        m, fd = HvdBootMsg(), ctypes.c_int(-1)
+        if self.core.hvd_boot_recv(self.h, ctypes.byref(m), ctypes.byref(fd)) != 0:
+            raise RuntimeError(f"bootstrap receive on rank {self.rank}: {self.core.hvd_boot_last_error().decode()}")
+        self.last = m
+        return int(m.tag), int(m.src_rank), int(fd.value)
 
     def close(self):
-        try:
-            self.sock.close()
-            os.unlink(self.path)
-        except OSError:
-            pass
+        if self.h:
+            self.core.hvd_boot_close(self.h)
+            self.h = None
 
 
 class PeerContext:
@@ -289,12 +306,13 @@ class PeerContext:
         tag = self._alloc_id
         for r in range(self.size):
             if r != self.rank:
-                self._fdx.send(r, fd.value, tag)
+                self._fdx.send(r, fd.value, tag, kind=BOOT_KIND_MEM, payload=size)
         handles = {self.rank: h.value}
         for _ in range(self.size - 1):
             t, src, pfd = self._fdx.recv()
-            if t != tag:
-                raise RuntimeError(f"symmetric alloc out of order: got tag {t}, expected {tag}")
+            if t != tag or self._fdx.last.kind != BOOT_KIND_MEM or self._fdx.last.payload != size:
+                raise RuntimeError(f"symmetric alloc out of order: rank {src} sent tag {t} / {self._fdx.last.payload} B, "
+                                   f"expected tag {tag} / {size} B (every rank must allocate in the same order)")
             ph = U64()
             self._chk_symm(core.hvd_symm_import(pfd, ctypes.byref(ph)), "cuMemImportFromShareableHandle")
             os.close(pfd)
@@ -328,7 +346,7 @@ class PeerContext:
                 if not created:
                     raise RuntimeError("cuMulticastCreate failed")
                 for r in range(1, self.size):
-                    self._fdx.send(r, fd.value, mtag)
+                    self._fdx.send(r, fd.value, mtag, kind=BOOT_KIND_MC, payload=size)
                 os.close(fd.value)
             else:
                 if not collectives.broadcast_object(None, 0):

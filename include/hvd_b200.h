@@ -87,6 +87,23 @@ int hvd_symm_mc_create(int ndev, long long bytes, unsigned long long* mc, int* f
 int hvd_symm_mc_add_device(unsigned long long mc, int device);
 int hvd_symm_mc_bind(unsigned long long mc, unsigned long long mem, long long bytes);
 
+/* Bootstrap channel (csrc/core/bootstrap.cpp): fixed-layout messages + POSIX fd passing (SCM_RIGHTS) between the
+ * ranks of one host - the start-up handle exchange behind hvd.init() (reference mnist_keras.py:30; Horovod:
+ * MPI_Bcast of the ncclUniqueId, message.cc / wire/message.fbs).  kind: 1 = memory handle, 2 = multicast handle. */
+typedef struct HvdBootMsg {
+  uint32_t magic;    /* 'HVDB' */
+  uint16_t version;
+  uint16_t kind;
+  int32_t src_rank;
+  int32_t tag;       /* ordinal of the symmetric allocation the handle belongs to */
+  uint64_t payload;  /* size in bytes of that allocation (consistency check) */
+} HvdBootMsg;
+void* hvd_boot_open(const char* dir, int rank, int size, double timeout_s);
+int hvd_boot_send(void* h, int dst, int kind, int tag, uint64_t payload, int fd /* -1: none */);
+int hvd_boot_recv(void* h, HvdBootMsg* out, int* fd);
+void hvd_boot_close(void* h);
+const char* hvd_boot_last_error(void);
+
 /* ------------------------------------------------------------------ libhvd_cuda.so */
 
 struct HvdCommCtx;   /* csrc/comm/comm.cuh  */

@@ -337,3 +337,32 @@ def test_dataset_batch_ring_reuses_slots_without_corrupting_recent_batches():
         for xr, yr in recent:                           # batches stay intact until their slot comes round again
             assert (xr[:len(yr), 0] == yr * 3).all()
     assert np.bincount(np.concatenate(total)).tolist() == [3] * 400
+
+
+def test_native_bootstrap_channel_passes_descriptors(tmp_path):
+    """csrc/core/bootstrap.cpp: two endpoints exchange a fixed-layout message with a file descriptor attached
+    (SCM_RIGHTS) - the start-up handle exchange of the symmetric arenas, without pickles."""
+    import os
+    from horovod_distributed_example_b200.parallel import peer as P
+    a = P._FdExchange(0, 2, f"test-{os.getpid()}", timeout_s=5.0)
+    b = P._FdExchange(1, 2, f"test-{os.getpid()}", timeout_s=5.0)
+    try:
+        f = tmp_path / "payload.txt"
+        f.write_text("hello from rank 0")
+        fd = os.open(str(f), os.O_RDONLY)
+        a.send(1, fd, tag=7, kind=P.BOOT_KIND_MEM, payload=4096)
+        os.close(fd)
+        tag, src, got = b.recv()
+        assert (tag, src) == (7, 0) and got >= 0
+        assert b.last.kind == P.BOOT_KIND_MEM and b.last.payload == 4096 and b.last.magic == 0x48564442
+        assert os.read(got, 64) == b"hello from rank 0"        # the SAME open file, in another endpoint
+        os.close(got)
+        b.send(0, -1, tag=9, kind=P.BOOT_KIND_MC)               # a message without a descriptor
+        tag, src, got = a.recv()
+        assert (tag, src, got) == (9, 1, -1)
+        import pytest
+        with pytest.raises(RuntimeError, match="receive"):      # nothing pending: the bounded receive gives up
+            a.recv()
+    finally:
+        a.close()
+        b.close()
