@@ -758,6 +758,29 @@ class MnistEngine:
         return g
 
     # ------------------------------------------------------------------ eval / predict
+    def _inference(self, B: int, probs: bool):
+        """Forward + head with dropout off, replayed from a CUDA graph per (batch size, probs) like the training
+        step (four launches: conv1, conv2+pool, dense1, head)."""
+        if not self.use_graph:
+            self._forward(B, False)
+            self._head(B, False, False, probs=probs)
+            return
+        key = ("inference", B, probs)
+        g = self._graphs.get(key)
+        if g is None:
+            import gc
+            gc.collect()
+            torch.cuda.synchronize(self.dev)
+            g = torch.cuda.CUDAGraph()
+            cap = torch.cuda.Stream(device=self.dev)
+            cap.wait_stream(torch.cuda.current_stream(self.dev))
+            with torch.cuda.graph(g, stream=cap, capture_error_mode="thread_local"):
+                self._forward(B, False)
+                self._head(B, False, False, probs=probs)
+            torch.cuda.current_stream(self.dev).wait_stream(cap)
+            self._graphs[key] = g
+        g.replay()
+
     def eval_step(self, x: torch.Tensor, y: torch.Tensor):
         B = x.shape[0]
         self.sync_params()
@@ -765,15 +788,17 @@ class MnistEngine:
             y = y.argmax(dim=1)
         self.x_in[:B].copy_(x.reshape(B, -1), non_blocking=True)
         self.y_in[:B].copy_(y.to(torch.int64), non_blocking=True)
-        self._forward(B, False)
-        self._head(B, False, False)
-        return self.state_f[3].clone(), self.state_f[4].clone()
+        self._inference(B, False)
+        out = self.state_f[3].clone(), self.state_f[4].clone()
+        self._ev_done[0].record(self._main())      # the next training batch staged into these buffers waits for us
+        return out
 
     def predict(self, x: torch.Tensor):
         B = x.shape[0]
         self.sync_params()
         self.x_in[:B].copy_(x.reshape(B, -1), non_blocking=True)
         self.y_in[:B].zero_()
-        self._forward(B, False)
-        self._head(B, False, False, probs=True)
-        return self.probs[:B].clone()
+        self._inference(B, True)
+        out = self.probs[:B].clone()
+        self._ev_done[0].record(self._main())
+        return out

@@ -215,15 +215,16 @@ def torchmodel_bn_vs_ddp():
         l1, l2 = float(l1.detach()), float(l2.detach())
         print(f"rank {r} step {i}: loss ours {l1:.5f} ddp {l2:.5f}", flush=True)
         assert abs(l1 - l2) < (1e-4, 1e-4, 1e-4, 5e-3, 5e-2)[i], (i, l1, l2)      # see the note below on the growth
-        if i == 2:
-            # parameters after 3 updates: a BatchNorm net at batch 8 amplifies the fp32 summation-order difference
-            # between the two allreduces by roughly 10x per step (1e-5 in the loss after one update, 1e-3 after
-            # four), so the tight parameter check sits here and the loss check covers the rest
+        if i in (1, 2):
+            # parameters after 2 and 3 updates: a BatchNorm net at batch 8 amplifies the fp32 summation-order
+            # difference between the two allreduces by roughly 10x per step (1e-5 in the loss after one update, 1e-3
+            # after four), so the tight parameter check sits early and the loss check covers the rest
             torch.cuda.synchronize()
+            bound = 1e-3 if i == 1 else 1e-2
             for (na, pa), (nb, pb) in zip(net.named_parameters(), ref_net.named_parameters()):
                 d = (pa - pb).abs().max().item()
                 worst = max(worst, d)
-                assert d < 1e-3 * max(1.0, pb.abs().max().item()), (na, d)
+                assert d < bound * max(1.0, pb.abs().max().item()), (i, na, d)
     torch.cuda.synchronize()
     cs = hvd.allgather_object(int(m.arena.checksum()))
     assert all(c == cs[0] for c in cs), cs
