@@ -67,7 +67,17 @@ def discover_env(env=None):
 
     Falls back to a singleton world when no launcher variables are present.
     """
-    env = os.environ if env is None else env
+    if env is None:
+        # the process environment: the native runtime core owns the contract table (csrc/core/runtime.cpp,
+        # hvd_core_discover_env); the loop below is its twin for explicit dicts and hosts without the library
+        core = _native_core()
+        if core is not None:
+            import ctypes
+            v = (ctypes.c_int * 4)()
+            if core.hvd_core_discover_env(v, None) != 0:
+                raise ValueError("launcher environment is inconsistent: rank outside [0, size)")
+            return int(v[0]), int(v[1]), int(v[2]), int(v[3])
+        env = os.environ
     for rk, sz, lr, ls in _ENV_CONTRACTS:
         if rk in env and sz in env:
             rank, size = int(env[rk]), int(env[sz])
@@ -77,6 +87,14 @@ def discover_env(env=None):
                 raise ValueError(f"{rk}={rank} out of range for {sz}={size}")
             return rank, size, local_rank, local_size
     return 0, 1, 0, 1
+
+
+def _native_core():
+    try:
+        from .ops import native
+        return native.core_lib(required=False)
+    except Exception:  # pragma: no cover - no toolchain and no prebuilt library
+        return None
 
 
 def _setup_logging(level: str):
@@ -106,7 +124,16 @@ def init(comm=None, *, backend: Optional[str] = None, device: Optional[str] = No
     if _state.initialized:
         return
     cfg = Config.from_env()
-    rank, size, local_rank, local_size = discover_env()
+    core = _native_core()
+    if core is not None:
+        # init state lives in the native runtime core (Horovod: operations.cc horovod_init / rank / size); C and
+        # C++ callers of the C ABI read the same values through hvd_core_rank() etc.
+        if core.hvd_core_init() != 0:
+            raise ValueError("launcher environment is inconsistent: rank outside [0, size)")
+        rank, size = core.hvd_core_rank(), core.hvd_core_size()
+        local_rank, local_size = core.hvd_core_local_rank(), core.hvd_core_local_size()
+    else:
+        rank, size, local_rank, local_size = discover_env()
     _state.rank, _state.size = rank, size
     _state.local_rank, _state.local_size = local_rank, local_size
     _state.cross_rank = rank // max(local_size, 1)
@@ -193,6 +220,9 @@ def shutdown() -> None:
             except Exception as e:  # pragma: no cover
                 log.debug("destroy_process_group failed: %s", e)
     _state.__init__()
+    core = _native_core()
+    if core is not None:
+        core.hvd_core_shutdown()
 
 
 def _require_init():

@@ -182,6 +182,20 @@ def _declare_core(lib):
     _sig(lib, "hvd_nvtx_push", c_i32, [c_cp])
     _sig(lib, "hvd_nvtx_pop", c_i32, [])
     _sig(lib, "hvd_nvtx_mark", None, [c_cp])
+    _sig(lib, "hvd_core_discover_env", c_i32, [P_I32, ctypes.POINTER(c_cp)])
+    _sig(lib, "hvd_core_init", c_i32, [])
+    _sig(lib, "hvd_core_is_initialized", c_i32, [])
+    _sig(lib, "hvd_core_rank", c_i32, [])
+    _sig(lib, "hvd_core_size", c_i32, [])
+    _sig(lib, "hvd_core_local_rank", c_i32, [])
+    _sig(lib, "hvd_core_local_size", c_i32, [])
+    _sig(lib, "hvd_core_launcher", c_cp, [])
+    _sig(lib, "hvd_core_shutdown", None, [])
+    _sig(lib, "hvd_registry_add", c_i32, [ctypes.POINTER(ctypes.c_uint64), c_i32, ctypes.c_uint64, ctypes.c_uint64, c_i32])
+    _sig(lib, "hvd_registry_find", c_i32, [ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)])
+    _sig(lib, "hvd_registry_peer_ptr", ctypes.c_uint64, [c_i32, c_i32, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)])
+    _sig(lib, "hvd_registry_count", c_i32, [])
+    _sig(lib, "hvd_registry_clear", None, [])
     _sig(lib, "hvd_h5_last_error", c_cp, [])
     _sig(lib, "hvd_h5w_create", c_vp, [])
     _sig(lib, "hvd_h5w_free", None, [c_vp])

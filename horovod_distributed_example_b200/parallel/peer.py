@@ -212,6 +212,7 @@ class PeerContext:
         self.backend = "emulated" if emulated else backend
         self.multicast = False
         self._buffers: List[SymmBuffer] = []
+        self._by_id = {}                     # native registry id -> SymmBuffer
         self._raw = []                       # (kind, handle/ptr, bytes) for teardown
         self._fdx: Optional[_FdExchange] = None
         self._alloc_id = 0
@@ -280,6 +281,12 @@ class PeerContext:
             from .. import collectives
             collectives.barrier()
         self._buffers.append(buf)
+        core = native.core_lib(required=False)
+        if core is not None:
+            # the native registry (csrc/core/runtime.cpp) knows where every rank's copy of this buffer is mapped
+            arr = (ctypes.c_uint64 * len(buf.ptrs))(*buf.ptrs)
+            buf.registry_id = core.hvd_registry_add(arr, len(buf.ptrs), buf.nbytes, buf.mc_ptr or 0, buf.local_index)
+            self._by_id[buf.registry_id] = buf
         return buf
 
     def _alloc_emulated(self, nbytes: int) -> SymmBuffer:
@@ -407,6 +414,11 @@ class PeerContext:
     def buffer_of(self, t: torch.Tensor):
         """Return (SymmBuffer, element offset) when ``t`` lives inside a symmetric buffer."""
         p = t.data_ptr()
+        core = native.core_lib(required=False)
+        if core is not None and self._by_id:
+            off = ctypes.c_uint64(0)
+            b = self._by_id.get(core.hvd_registry_find(p, ctypes.byref(off)))
+            return (b, off.value // 4) if b is not None else (None, 0)
         for b in self._buffers:
             base = b.ptrs[b.local_index]
             if base <= p < base + b.nbytes:
@@ -600,6 +612,10 @@ class PeerContext:
         except Exception:
             pass
         self._buffers.clear()
+        self._by_id.clear()
+        core = native.core_lib(required=False)
+        if core is not None:
+            core.hvd_registry_clear()
         if self._fdx is not None:
             self._fdx.close()
         # VMM/IPC mappings are released with the process; explicit unmap order across ranks is

@@ -87,6 +87,26 @@ int hvd_symm_mc_create(int ndev, long long bytes, unsigned long long* mc, int* f
 int hvd_symm_mc_add_device(unsigned long long mc, int device);
 int hvd_symm_mc_bind(unsigned long long mc, unsigned long long mem, long long bytes);
 
+/* Process-level runtime state (csrc/core/runtime.cpp) - Horovod's C API horovod_init / rank / size / local_rank /
+ * shutdown behind hvd.init(), hvd.rank(), hvd.size(), hvd.local_rank() (reference mnist_keras.py:30,35,42).
+ * hvd_core_init reads the launcher's environment (HVD_*, OMPI_COMM_WORLD_*, PMI_*, torchrun; none = a world of one);
+ * the getters return -1 before it.  The registry records where every rank's copy of each symmetric buffer is mapped
+ * in this process (what the collective kernels address); hvd_registry_find maps a local address back to its buffer. */
+int hvd_core_discover_env(int* out4, const char** contract);
+int hvd_core_init(void);
+int hvd_core_is_initialized(void);
+int hvd_core_rank(void);
+int hvd_core_size(void);
+int hvd_core_local_rank(void);
+int hvd_core_local_size(void);
+const char* hvd_core_launcher(void);
+void hvd_core_shutdown(void);
+int hvd_registry_add(const uint64_t* ptrs, int n, uint64_t bytes, uint64_t mc_ptr, int local_index);
+int hvd_registry_find(uint64_t p, uint64_t* byte_offset);
+uint64_t hvd_registry_peer_ptr(int id, int r, uint64_t* mc_ptr, uint64_t* bytes);
+int hvd_registry_count(void);
+void hvd_registry_clear(void);
+
 /* Bootstrap channel (csrc/core/bootstrap.cpp): fixed-layout messages + POSIX fd passing (SCM_RIGHTS) between the
  * ranks of one host - the start-up handle exchange behind hvd.init() (reference mnist_keras.py:30; Horovod:
  * MPI_Bcast of the ncclUniqueId, message.cc / wire/message.fbs).  kind: 1 = memory handle, 2 = multicast handle. */

@@ -65,3 +65,35 @@ def test_size1_collectives_are_identity(hvd_single):
     assert torch.equal(hvd_single.allreduce(t), t)
     assert torch.equal(hvd_single.broadcast(t, 0), t)
     assert hvd_single.allreduce(3.0) == 3.0
+
+
+def test_native_runtime_core_state_and_registry(monkeypatch):
+    """csrc/core/runtime.cpp: the C API behind hvd.init()/rank()/size() (Horovod's horovod_init/horovod_rank/...)
+    reads the launcher contracts itself, and the registry maps a local address back to its symmetric buffer."""
+    import ctypes
+    from horovod_distributed_example_b200.ops import native
+    core = native.core_lib()
+    core.hvd_core_shutdown()
+    assert core.hvd_core_rank() == -1 and core.hvd_core_size() == -1            # before init, like Horovod's C API
+    for k in ("HVD_RANK", "HVD_SIZE", "RANK", "WORLD_SIZE", "PMI_RANK", "PMI_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("OMPI_COMM_WORLD_RANK", "3")
+    monkeypatch.setenv("OMPI_COMM_WORLD_SIZE", "8")
+    monkeypatch.setenv("OMPI_COMM_WORLD_LOCAL_RANK", "3")
+    monkeypatch.setenv("OMPI_COMM_WORLD_LOCAL_SIZE", "8")
+    assert core.hvd_core_init() == 0 and core.hvd_core_init() == 0             # idempotent
+    assert (core.hvd_core_rank(), core.hvd_core_size(), core.hvd_core_local_rank()) == (3, 8, 3)
+    assert core.hvd_core_launcher() == b"openmpi"
+    monkeypatch.setenv("HVD_RANK", "9")
+    monkeypatch.setenv("HVD_SIZE", "4")
+    v = (ctypes.c_int * 4)()
+    assert core.hvd_core_discover_env(v, None) == -1                            # rank outside [0, size)
+    core.hvd_core_shutdown()
+    ptrs = (ctypes.c_uint64 * 2)(0x10000, 0x90000)
+    bid = core.hvd_registry_add(ptrs, 2, 0x4000, 0, 1)
+    off = ctypes.c_uint64(0)
+    assert core.hvd_registry_find(0x90100, ctypes.byref(off)) == bid and off.value == 0x100
+    assert core.hvd_registry_find(0x10100, ctypes.byref(off)) == 0              # the peer's copy is not a local address
+    assert core.hvd_registry_peer_ptr(bid, 0, None, None) == 0x10000
+    core.hvd_registry_clear()
+    assert core.hvd_registry_count() == 0
