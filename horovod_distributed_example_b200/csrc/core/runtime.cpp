@@ -116,7 +116,9 @@ extern "C" int hvd_registry_add(const uint64_t* ptrs, int n, uint64_t bytes, uin
 // Which registered buffer does the LOCAL address `p` fall into?  Returns its id (and the byte offset), 0 if none.
 extern "C" int hvd_registry_find(uint64_t p, uint64_t* byte_offset) {
   std::lock_guard<std::mutex> lk(g_mu);
-  for (const SymmEntry& e : g_registry) {
+  // newest first: an address range can be registered again after its previous owner was released
+  for (auto it = g_registry.rbegin(); it != g_registry.rend(); ++it) {
+    const SymmEntry& e = *it;
     const uint64_t base = e.ptrs[(size_t)e.local_index];
     if (p >= base && p < base + e.bytes) {
       if (byte_offset) *byte_offset = p - base;
@@ -124,6 +126,13 @@ extern "C" int hvd_registry_find(uint64_t p, uint64_t* byte_offset) {
     }
   }
   return 0;
+}
+
+extern "C" int hvd_registry_remove(int id) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (size_t i = 0; i < g_registry.size(); i++)
+    if (g_registry[i].id == id) { g_registry.erase(g_registry.begin() + (long)i); return 0; }
+  return -1;
 }
 
 // Address of rank r's copy of buffer `id` (0 if unknown); *mc_ptr / *bytes may be NULL.

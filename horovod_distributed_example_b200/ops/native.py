@@ -194,6 +194,7 @@ def _declare_core(lib):
     _sig(lib, "hvd_registry_add", c_i32, [ctypes.POINTER(ctypes.c_uint64), c_i32, ctypes.c_uint64, ctypes.c_uint64, c_i32])
     _sig(lib, "hvd_registry_find", c_i32, [ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)])
     _sig(lib, "hvd_registry_peer_ptr", ctypes.c_uint64, [c_i32, c_i32, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)])
+    _sig(lib, "hvd_registry_remove", c_i32, [c_i32])
     _sig(lib, "hvd_registry_count", c_i32, [])
     _sig(lib, "hvd_registry_clear", None, [])
     _sig(lib, "hvd_h5_last_error", c_cp, [])

@@ -418,7 +418,9 @@ class PeerContext:
         if core is not None and self._by_id:
             off = ctypes.c_uint64(0)
             b = self._by_id.get(core.hvd_registry_find(p, ctypes.byref(off)))
-            return (b, off.value // 4) if b is not None else (None, 0)
+            if b is not None:
+                return b, off.value // 4
+            # (the registry is per process; an entry of another context may shadow nothing of ours - fall through)
         for b in self._buffers:
             base = b.ptrs[b.local_index]
             if base <= p < base + b.nbytes:
@@ -612,10 +614,11 @@ class PeerContext:
         except Exception:
             pass
         self._buffers.clear()
-        self._by_id.clear()
         core = native.core_lib(required=False)
         if core is not None:
-            core.hvd_registry_clear()
+            for bid in self._by_id:
+                core.hvd_registry_remove(bid)
+        self._by_id.clear()
         if self._fdx is not None:
             self._fdx.close()
         # VMM/IPC mappings are released with the process; explicit unmap order across ranks is

@@ -102,7 +102,8 @@ int hvd_core_local_size(void);
 const char* hvd_core_launcher(void);
 void hvd_core_shutdown(void);
 int hvd_registry_add(const uint64_t* ptrs, int n, uint64_t bytes, uint64_t mc_ptr, int local_index);
-int hvd_registry_find(uint64_t p, uint64_t* byte_offset);
+int hvd_registry_find(uint64_t p, uint64_t* byte_offset);   /* newest matching entry */
+int hvd_registry_remove(int id);
 uint64_t hvd_registry_peer_ptr(int id, int r, uint64_t* mc_ptr, uint64_t* bytes);
 int hvd_registry_count(void);
 void hvd_registry_clear(void);
