@@ -456,3 +456,13 @@ extern "C" int hvd_allgather_launch(const HvdCommCtx* c, const HvdAllgatherArgs*
   }
   return (int)cudaLaunchKernelEx(&cfg, hvd_allgather_kernel, *c, *a);
 }
+
+// sizeof of the argument structs, in the order HvdCommCtx, HvdRsPush, HvdParamWait, HvdTailArgs, HvdAllgatherArgs:
+// the ctypes mirrors (parallel/peer.py, parallel/pipeline.py) are checked against these in the CPU tests.
+extern "C" void hvd_pipeline_struct_sizes(int* out5) {
+  out5[0] = (int)sizeof(HvdCommCtx);
+  out5[1] = (int)sizeof(HvdRsPush);
+  out5[2] = (int)sizeof(HvdParamWait);
+  out5[3] = (int)sizeof(HvdTailArgs);
+  out5[4] = (int)sizeof(HvdAllgatherArgs);
+}

@@ -366,3 +366,21 @@ def test_native_bootstrap_channel_passes_descriptors(tmp_path):
     finally:
         a.close()
         b.close()
+
+
+def test_pipelined_step_is_only_offered_for_even_tile_splits():
+    """parallel/pipeline.py: the 72 row tiles of dense_1/kernel (9216 rows) must split evenly over the ranks; other
+    world sizes keep the bucket kernels."""
+    from horovod_distributed_example_b200.parallel import pipeline as PL
+    assert [n for n in range(1, 9) if PL.supported(n, 9216)] == [1, 2, 3, 4, 6, 8]
+    assert not PL.supported(2, 9216 + 64)                       # not whole 128-row tiles
+    import ctypes
+    # the ctypes argument structs mirror the C side field for field: compare sizes with the library's own sizeof
+    from horovod_distributed_example_b200.ops import native
+    from horovod_distributed_example_b200.parallel import peer as P
+    lib = native.cuda_lib(required=False)
+    if lib is not None:
+        out = (ctypes.c_int * 5)()
+        lib.hvd_pipeline_struct_sizes(out)
+        assert list(out) == [ctypes.sizeof(P.HvdCommCtx), ctypes.sizeof(PL.HvdRsPush), ctypes.sizeof(PL.HvdParamWait),
+                             ctypes.sizeof(PL.HvdTailArgs), ctypes.sizeof(PL.HvdAllgatherArgs)]
