@@ -21,7 +21,7 @@ SPECS = [("d2/b", (10,)), ("d2/k", (128, 10)), ("d1/b", (128,)), ("d1/k", (ROWS,
          ("c2/k", (3, 3, 32, 64)), ("c1/b", (32,)), ("c1/k", (3, 3, 1, 32))]
 
 
-@pytest.mark.parametrize("N,flag_kernel", [(1, 1), (2, 1), (4, 1), (2, 0)])
+@pytest.mark.parametrize("N,flag_kernel", [(1, 1), (2, 1), (3, 1), (4, 1), (2, 0)])
 @pytest.mark.parametrize("opt_name", ["adadelta", "adam"])
 def test_emulated_pipelined_step_matches_cpu_oracle(N, flag_kernel, opt_name, monkeypatch):
     _need_gpu()
