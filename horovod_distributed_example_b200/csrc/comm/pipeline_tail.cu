@@ -50,7 +50,7 @@ struct HvdTailArgs {
                                   // (written here, stamped on the peers by the all-gather, awaited by readers)
   const float* hyper;             // device fp32[8]
   float scale;                    // 1/N
-  int kind, parity, ll_ctas, use_mc;
+  int kind, parity, ll_ctas, use_mc;       // (use_mc: unused by the tail since the all-gather left it; kept for layout)
   // HVD_TIMELINE / profiling: ring of 64 records x 16 %globaltimer stamps (ns), indexed by epoch & 63, or null.
   //   [0] LL CTA 0 entered   [1] LL CTA 0 pushed its packets   [2] LL CTA 0 has every peer's packets   [3] LL CTA 0 done
   //   [4] first shard CTA entered  [5] its tiles were there  [7] it is done   ([10], [11]: hvd_allgather_kernel)

@@ -249,8 +249,9 @@ class MnistEngine:
         # vs 134 / 115 with 16 / 24 SMs reserved), so tail is the default; overlap stays selectable.
         # HVD_BUCKET_MODE=pipelined (default): no bucket kernels at all.  dense1's dW GEMM pushes its tiles to
         # their owner ranks while the conv backward runs, ONE tail kernel does the barrier-free LL allreduce +
-        # update of the small tensors and the owners' reduce + update + store of the big one, and the next
-        # step's dense1 forward waits on a counter instead of anybody sitting in an exit barrier
+        # update of the small tensors and the owners' reduce + update of the big one, the next step's conv1 kernel
+        # delivers the updated rows to the other replicas, and that
+        # step's conv2 kernel waits for the delivery flags instead of anybody sitting in an exit barrier
         # (parallel/pipeline.py).  Needs the 72 row tiles of dense_1/kernel to split evenly over the ranks.
         from ..parallel import pipeline as pipe_mod
         mode = os.environ.get("HVD_BUCKET_MODE", "pipelined")

@@ -5,9 +5,11 @@ into on the fused MNIST engine when the world size divides the 72 row tiles of t
 
 * the GEMM that produces that kernel's gradient (98% of the bytes) pushes each output tile into the receive
   area of the rank that owns those rows while the conv backward is still running (``tc_gemm`` EPI_RS_PUSH);
-* ONE tail kernel per step does the rest: a barrier-free LL one-shot allreduce + update of the ~80 KB of small
-  tensors, and the owner's reduce + update + store-to-every-replica of its rows;
-* nobody waits in an exit barrier: the next step's first reader of the big weights waits on a counter.
+* ONE tail kernel per step: a barrier-free LL one-shot allreduce + update of the ~80 KB of small tensors, and the
+  owner's reduce + update of its rows (parameters and optimizer state of those rows live with their owner);
+* the updated rows reach the other replicas under the NEXT step's conv forward (the first blocks of its conv1
+  kernel copy them and stamp version flags; a flush does the same with a stand-alone kernel), and the first
+  reader of the big weights waits on those flags - nobody waits in an exit barrier.
 
 This object owns the symmetric receive buffers and fills the argument structs; the engine launches through it.
 It also works on an emulated context (``PeerContext.emulate(n)``: n ranks on one GPU, one cooperative launch
@@ -286,8 +288,8 @@ class PipelinedStep:
 
     def materialize_state(self) -> None:
         """Pull the optimizer-state rows owned by the other ranks into this rank's arena (one-sided peer
-        reads; called before a checkpoint is written).  The caller has already waited on the ready counter,
-        which every owner bumps only after its state writes are visible."""
+        reads; called before a checkpoint is written).  The caller has already waited for the peers' version flags,
+        which every owner stamps only after its tail kernel - and with it its state writes - has completed."""
         ar = self.arena
         me = 0 if self.ctx.emulated else self.ctx.rank
         for r in range(self.n):
