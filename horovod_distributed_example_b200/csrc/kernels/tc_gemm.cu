@@ -23,6 +23,7 @@
 //                 their owners (version flags stamped by the all-gather CTAs that run beside the conv forward),
 //                 instead of anybody sitting in an exit barrier.
 #include "comm/pipeline.cuh"
+#include "mnist_head.cuh"
 #include "tc_common.cuh"
 
 namespace {
@@ -35,7 +36,11 @@ constexpr int STAGES = 4;
 // dropped-out activations, row = sample, column = flat (ph,pw,c)) is routed through the mask byte
 // written by conv2_fprop: scaled by 1/keep where live, placed at the arg-max of its 2x2 window,
 // zeros at the other three positions - MaxPool/Dropout/ReLU backward fused into the dgrad epilogue.
-enum Epilogue { EPI_STORE = 0, EPI_ATOMIC_ADD = 1, EPI_BIAS_RELU = 2, EPI_UNPOOL = 3, EPI_RS_PUSH = 4 };
+// EPI_SPLITK_HEAD: split-K accumulation (as EPI_ATOMIC_ADD) followed, in the same kernel, by the classifier head
+// (mnist_head.cuh): every slice CTA adds its partial tile, takes a ticket on a device counter, waits until all
+// slices of this launch have arrived, and the first ceil(B/8) CTAs then run the head on 8 rows each - the
+// Dense(128) forward and everything up to the Dense(128) pre-activation gradient without a kernel boundary.
+enum Epilogue { EPI_STORE = 0, EPI_ATOMIC_ADD = 1, EPI_BIAS_RELU = 2, EPI_UNPOOL = 3, EPI_RS_PUSH = 4, EPI_SPLITK_HEAD = 5 };
 
 struct GemmParams {
   int M, N, K;
@@ -49,6 +54,8 @@ struct GemmParams {
   float scale;                           // EPI_UNPOOL: 1/keep
   HvdRsPush rs;                          // EPI_RS_PUSH
   HvdParamWait wait;                     // flags == nullptr: no wait
+  mnist::HeadParams head;                // EPI_SPLITK_HEAD
+  unsigned long long* head_counter;      // EPI_SPLITK_HEAD: arrival tickets, never reset (one per slice CTA per launch)
 };
 
 template <int BN>
@@ -207,7 +214,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           T[rl * 32 + (((c >> 2) + j) ^ lane)] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
       } else if (row < p.M) {
         float* d = p.D + (long long)row * p.ldd + n0 + c;
-        if (p.epilogue == EPI_ATOMIC_ADD) {
+        if (p.epilogue == EPI_ATOMIC_ADD || p.epilogue == EPI_SPLITK_HEAD) {
           if (n0 + c + 32 <= p.N && (p.ldd & 3) == 0) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) tc::red_add_f4(d + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
@@ -254,6 +261,32 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   }
+  if (warp >= 4 && p.epilogue == EPI_SPLITK_HEAD) {
+    // all 8 epilogue warps.  This CTA's partial sums are in L2 (red.add) before its ticket is taken ...
+    __threadfence();
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x == 128) {
+      __threadfence();
+      const unsigned long long ks = gridDim.z;
+      const unsigned long long old = atomicAdd(p.head_counter, 1ull);
+      const unsigned long long target = (old / ks + 1ull) * ks;       // all slices of THIS launch
+      unsigned spins = 0;
+      for (;;) {
+        unsigned long long now;
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(now) : "l"(p.head_counter) : "memory");
+        if (now >= target) break;
+        __nanosleep(32);
+        if (++spins > (1u << 24)) { asm volatile("trap;"); }           // a lost slice must trap, not hang the GPU
+      }
+      __threadfence();
+    }
+    // ... and every slice's sums are there before anybody reads them (the slices are co-resident: k_split <= SMs)
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if ((int)blockIdx.z * mnist::HEAD_ROWS < p.head.B) {
+      mnist::HeadSmem& sm = *reinterpret_cast<mnist::HeadSmem*>(smem);    // the operand ring is idle by now
+      mnist::head_rows(p.head, blockIdx.z, threadIdx.x - 128, sm, [] { asm volatile("bar.sync 1, 256;" ::: "memory"); });
+    }
+  }
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 2) tc::tmem_dealloc<BN>(tmem);
@@ -297,7 +330,9 @@ extern "C" int hvd_tc_gemm_ex(const float* A, const float* B, float* D, int M, i
     else { dims[0] = N; dims[1] = K; str[0] = (uint64_t)N * 4; box[0] = 32; box[1] = BK; }
     if (tc::make_tmap(&tb, B, 2, dims, str, box, b_mn != 0)) return -3;
   }
-  GemmParams p{M, N, K, k_split, D, ldd ? ldd : (long long)N, bias, epilogue, lbo_a, sbo_a, lbo_b, sbo_b, mask, scale, {}, {}};
+  if (epilogue == EPI_SPLITK_HEAD) return -6;          // only through hvd_dense1_fwd_head
+  GemmParams p{M, N, K, k_split, D, ldd ? ldd : (long long)N, bias, epilogue, lbo_a, sbo_a, lbo_b, sbo_b, mask, scale, {}, {},
+               {}, nullptr};
   if (rs) p.rs = *rs;
   if (wait) p.wait = *wait;
   cudaStream_t st = (cudaStream_t)stream;
@@ -314,4 +349,30 @@ extern "C" int hvd_tc_gemm(const float* A, const float* B, float* D, int M, int 
                            float scale) {
   return hvd_tc_gemm_ex(A, B, D, M, N, K, a_mn, b_mn, bn, k_split, epilogue, bias, ldd, stream, lbo_a, sbo_a, lbo_b,
                         sbo_b, mask, scale, nullptr, nullptr);
+}
+
+// Dense(128) forward + classifier head in ONE launch (reference layers mnist_keras.py:79-81, loss/metric :89-91):
+//   h_pre[B][128] += x[B][K] * W[K][128] over k_split slices of K, then hvd_head's work on the reduced sums
+// (arguments as hvd_head; h_pre must be zero on entry and is zero again on exit).  `counter` is a device
+// uint64 that starts at 0 and is never reset.  Needs k_split * 8 >= B (one head group of 8 rows per slice CTA)
+// and k_split <= 148 (the slices wait for each other).  wait: as hvd_tc_gemm_ex (may be NULL).
+extern "C" int hvd_dense1_fwd_head(const float* x, const float* W, int B, int K, int k_split, float* h_pre, const float* b1,
+                                   const float* w2, const float* b2, const long long* labels, float* dh_pre, float* g_w2,
+                                   float* g_b2, float* g_b1, float* probs, void* step_state, int training, int backward,
+                                   float keep, unsigned long long* counter, const HvdParamWait* wait, void* stream) {
+  if (B < 1 || B > BM || K < 1 || (K & 3) || k_split < 1 || k_split > 148 || k_split * mnist::HEAD_ROWS < B || !counter) return -1;
+  CUtensorMap ta, tb;
+  {
+    uint64_t dims[2], str[1];
+    uint32_t box[2];
+    dims[0] = K; dims[1] = B; str[0] = (uint64_t)K * 4; box[0] = BK; box[1] = BM;
+    if (tc::make_tmap(&ta, x, 2, dims, str, box, false)) return -2;
+    dims[0] = 128; dims[1] = K; str[0] = 128 * 4; box[0] = 32; box[1] = BK;
+    if (tc::make_tmap(&tb, W, 2, dims, str, box, true)) return -3;
+  }
+  GemmParams p{B, 128, K, k_split, h_pre, 128, nullptr, EPI_SPLITK_HEAD, 0, 0, 0, 0, nullptr, 1.0f, {}, {}, {}, counter};
+  if (wait) p.wait = *wait;
+  p.head = mnist::HeadParams{B, training, backward, mnist::HEAD_ROWS, keep, h_pre, b1, w2, b2, labels, dh_pre, g_w2, g_b2,
+                             g_b1, probs, reinterpret_cast<mnist::StepState*>(step_state)};
+  return launch<128, false, true>(ta, tb, p, (cudaStream_t)stream);
 }

@@ -60,6 +60,8 @@ def _declare(lib):
     lib.hvd_conv2_fprop_ex.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, cf, ci, vp, vp]
     lib.hvd_conv2_fprop.restype = ci
     lib.hvd_conv2_fprop.argtypes = [vp, vp, vp, vp, vp, vp, ci, ci, cf, ci, vp]
+    lib.hvd_dense1_fwd_head.restype = ci
+    lib.hvd_dense1_fwd_head.argtypes = [vp, vp, ci, ci, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, cf, vp, vp, vp]
     lib.hvd_head.restype = ci
     lib.hvd_head.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, cf, vp]
     lib.hvd_memcpy_async.restype = ci
@@ -228,6 +230,9 @@ class MnistEngine:
         self._conv1_bps = 8
         self._tl_offset, self._tl_done, self._tl_active = None, 0, False
         self._hyper_pushed = False
+        # HVD_FUSE_HEAD=1: dense1 forward + head as one launch (EPI_SPLITK_HEAD)
+        self._fuse_head = os.environ.get("HVD_FUSE_HEAD", "0") == "1"
+        self._head_ctr = torch.zeros(1, dtype=torch.int64, device=dev)
         # where the all-gather of the updated rows runs: "conv1" = as the first blocks of the next step's conv1
         # forward kernel (default), "start" = a separate small kernel forked at the start of the next step,
         # "tail" = right behind the tail kernel (exposed; A/B only)
@@ -309,7 +314,7 @@ class MnistEngine:
             comm_launches = 1 + (1 if (self.pipe.flag_kernel and self.pipe.n > 1) else 0)
         else:
             comm_launches = len(self.fused.buckets) if self.fused is not None else 0
-        self.launches_per_step = (7 if self._fused_bwd else 8) + comm_launches
+        self.launches_per_step = (7 if self._fused_bwd else 8) - (1 if self._fuse_head else 0) + comm_launches
 
     # ------------------------------------------------------------------ helpers
     @staticmethod
@@ -451,10 +456,25 @@ class MnistEngine:
     def _part_a(self, B: int, which: int):
         self._forward_conv(B, True, which)
 
+    def _dense_head_fused(self, B: int, which: int):
+        """dense1 forward (split-K) + the head in ONE launch (tc_gemm EPI_SPLITK_HEAD): the slice CTAs wait for each
+        other on a ticket counter and the first 16 of them run the head on 8 rows each."""
+        gp = lambda k, sh: self._g(k, sh, which).data_ptr()                              # noqa: E731
+        w = self.pipe.param_wait() if (self.pipe is not None and self._wait_in == "d1fwd") else None
+        self._chk(self.lib.hvd_dense1_fwd_head(
+            self.p2.data_ptr(), self._p("f1", "kernel").data_ptr(), B, 9216, int(os.environ.get('HVD_D1_KSPLIT', 32)),
+            self.h_pre.data_ptr(), self._p("f1", "bias").data_ptr(), self._p("f2", "kernel").data_ptr(),
+            self._p("f2", "bias").data_ptr(), self.y_bufs[which].data_ptr(), self.dh_pre.data_ptr(), gp("f2", "kernel"),
+            gp("f2", "bias"), gp("f1", "bias"), None, self.state.data_ptr(), 1, 1, self.keep2,
+            self._head_ctr.data_ptr(), ctypes.addressof(w) if w is not None else None, self._s()), "dense1_fwd_head")
+
     def _part_b(self, B: int, which: int):
         main = torch.cuda.current_stream(self.dev)
-        self._forward_dense(B)
-        self._head(B, True, True, which)
+        if self._fuse_head and not ({"d1fwd", "head"} & self._SKIP):
+            self._dense_head_fused(B, which)
+        else:
+            self._forward_dense(B)
+            self._head(B, True, True, which)
         self._ev_fork.record(main)
         if self.pipe is not None:
             # GEMM -> reduce-scatter in one kernel: every 128-row tile goes to its owner's receive area (local

@@ -191,6 +191,15 @@ int hvd_globaltimer_probe(unsigned long long* out, void* stream);   /* one %glob
  * and any small tensor-level hvd.allreduce. */
 int hvd_ll_allreduce_launch(const struct HvdCommCtx* c, const struct HvdLLArgs* a, void* stream, int emulate_ranks);
 
+/* Dense(128) forward + classifier head in ONE launch (reference layers mnist_keras.py:79-81, loss / metric :89-91):
+ * h_pre[B][128] += x[B][K] * W[K][128] over k_split slices of K; the slice CTAs then wait for each other on `counter`
+ * (device uint64, starts at 0, never reset) and the first ceil(B/8) of them do hvd_head's work on 8 rows each.
+ * Needs B <= 128, k_split * 8 >= B, k_split <= 148; h_pre zero on entry (and zero again on exit). */
+int hvd_dense1_fwd_head(const float* x, const float* W, int B, int K, int k_split, float* h_pre, const float* b1,
+                        const float* w2, const float* b2, const long long* labels, float* dh_pre, float* g_w2,
+                        float* g_b2, float* g_b1, float* probs, void* step_state, int training, int backward, float keep,
+                        unsigned long long* counter, const struct HvdParamWait* wait, void* stream);
+
 /* Fused MNIST-CNN engine kernels (reference model mnist_keras.py:71-81). */
 /* conv1 forward; also the step prologue: clears [zero_a, +n_a) and [zero_b, +n_b) (the gradient ranges
  * later kernels red.add into; multiples of 4 floats, may be NULL), clears the per-step loss/accuracy words

@@ -262,6 +262,7 @@ def _models(rate1, rate2, opt_name):
 @pytest.mark.parametrize("opt_name,env", [("adadelta", {}), ("adam", {}),
                                           ("adadelta", {"HVD_BUCKET_MODE": "overlap"}),        # bucket 0 on a side stream
                                           ("adam", {"HVD_FUSED_BWD": "1"}),                     # wgrad + dgrad as one kernel
+                                          ("adadelta", {"HVD_FUSE_HEAD": "1"}),                 # dense1 fwd + head as one kernel
                                           ("adadelta", {"HVD_BUCKET_MODE": "overlap", "HVD_RESERVE_SMS": "0"})])
 def test_engine_matches_torch_oracle_without_dropout(opt_name, env, monkeypatch):
     """Whole fused step (CUDA graph, fused update) vs the torch-autograd oracle, dropout rate 0 - in the default
