@@ -196,7 +196,8 @@ def reference_arm(args):
             import tensorflow  # noqa: F401
         except Exception as e:
             why = f"baseline/_ref present but not importable: {type(e).__name__}: {e}"
-    print(json.dumps({"impl": "reference", "unavailable": why}))
+    if int(os.environ.get("RANK", 0)) == 0:          # launched under torchrun for N > 1: one line, from rank 0
+        print(json.dumps({"impl": "reference", "unavailable": why}))
     return 0
 
 
